@@ -1,0 +1,199 @@
+"""Host-side mirror of the reference's `SonataXAffinityTrainer` inference surface on the CUDA path.
+
+Reference: models/affinity_module.py -- `lift_lseg_features` (:348-453), `evaluate_scene` (:1490-1608).
+The 2-D VLM (X-Decoder / LSeg) and the Sonata teacher are out of scope: the
+per-view 2-D features are supplied by a `view_features` provider as channels-last device tensors.
+
+Two entry styles:
+  * `evaluate_scene(batch_data)`        -- the reference's positional 20-tuple (CPU tensors), returns the same
+                                           dict {"scene_features", "text_features", "logit_scale"};
+  * `run_scene(SceneInputs)`            -- the B200-first form: cameras + depth instead of precomputed pixel
+                                           lists, fused projection/gather, everything stays on the device,
+                                           returns labels + IoU histograms.
+Internally voxels are processed in Morton order; every exposed index tensor is in the reference's order.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from . import ops
+from .student import AffinityPredictor
+
+
+@dataclass
+class SceneInputs:
+    """Device-resident inputs of one scene for `run_scene` (data layout)."""
+    coords: torch.Tensor           # [N,3] float64 or float32 world xyz (float64 is what the .pth files hold)
+    coords_f32: torch.Tensor       # [N,3] float32 (scene_coords of the batch tuple; hole fills use it)
+    gauss: torch.Tensor            # [N,6] float32 rgb | normal
+    voxel_coords: torch.Tensor     # [M,3] int32
+    p2v: torch.Tensor              # [N] int32 point -> voxel (scene_inds_reconstruct)
+    extent: tuple                  # (ex, ey, ez) exclusive bound of voxel_coords (host ints)
+    w2c: torch.Tensor              # [V,16] float64
+    intr: torch.Tensor             # [V,4] float64
+    depth: Optional[torch.Tensor]  # [V,H,W] float64/float32
+    feat: torch.Tensor             # [V,H,W,D] bf16/float32 channels-last 2-D features
+    image_dim: tuple               # (W, H)
+    cut: int
+    vis_thres: float
+    labels: Optional[torch.Tensor] = None   # [N] int64
+
+
+class SonataXAffinityTrainer:
+    """Inference half of the reference class of the same name.  (`GeoPurifyB200` is an alias.)"""
+
+    K = 96                        # models/affinity_module.py:1492
+    affinity_sharpen_factor = 20  # :1493
+    n_pool = 19                   # :1584-1587
+
+    def __init__(self, cfg=None, text_features=None, logit_scale=100.0, view_features=None, student=None,
+                 feature_dim=512, K=None, n_pool=None, sharpen=None, min_visible=400, fill_cell=0.05,
+                 device="cuda"):
+        L.require_cuda()
+        self.cfg = cfg
+        self.device = torch.device(device)
+        self.feature_dim = feature_dim
+        self.affinity_student = student if student is not None else AffinityPredictor(
+            input_dim=feature_dim + 6, embed_dim=128, hidden_dim=512)          # :266-272
+        self.text_features = None if text_features is None else torch.as_tensor(text_features).float().to(self.device)
+        self.logit_scale = float(logit_scale)
+        self.view_features = view_features
+        self.use_lseg = True
+        if K is not None:
+            self.K = K
+        if n_pool is not None:
+            self.n_pool = n_pool
+        if sharpen is not None:
+            self.affinity_sharpen_factor = sharpen
+        self.min_visible = min_visible
+        self.fill_cell = fill_cell
+        self.last = {}
+
+    def eval(self):
+        return self
+
+    # ------------------------------------------------------------------ stage 1b (reference tuple form)
+    @staticmethod
+    def pixels_from_batch(batch_data, W):
+        """x_labels / y_labels / mask_2ds of the 20-tuple -> pix [V,N] int32 on the device
+        (dataset/data_loader_ablation.py:348-353, collate :446-459)."""
+        scene_coords = batch_data[0]
+        x_labels, y_labels, mask_2ds = batch_data[12], batch_data[13], batch_data[14]
+        n = scene_coords.shape[0]
+        v = mask_2ds.shape[0] // n
+        mask = mask_2ds[:, 1].cuda().bool()
+        pix = torch.full((v * n,), -1, dtype=torch.int32, device="cuda")
+        lin = (x_labels.cuda().long() * W + y_labels.cuda().long()).to(torch.int32)
+        if int(mask.sum()) != lin.shape[0]:
+            raise L.GeoPurifyError("mask_2ds and x_labels disagree (a visible point with row or col 0 was dropped; "
+                                   "the reference needs cut_boundary >= 1)")
+        pix[mask] = lin
+        return pix.view(v, n)
+
+    @torch.no_grad()
+    def lift_lseg_features(self, batch_data, max_batch_size=24):
+        """Gather + mean over views + 1-NN fill (models/affinity_module.py:404-453).  `self.view_features(batch_data)`
+        supplies the [V,H,W,D] channels-last maps the LSeg forward would have produced."""
+        scene_coords = batch_data[0]
+        feat = self.view_features(batch_data)
+        v, h, w, d = feat.shape
+        pix = self.pixels_from_batch(batch_data, w)
+        out, seen = ops.lift_mean_pix(pix, None, feat, h, w)
+        xyz = scene_coords.float().cuda().contiguous()
+        nn = ops.nn1_fill(xyz, seen, self.fill_cell)
+        ops.copy_rows(out, d, nn)
+        return out, self.text_features, self.logit_scale
+
+    # ------------------------------------------------------------------ stages 2-3
+    @torch.no_grad()
+    def purify(self, lifted, gauss, voxel_coords_i32, p2v_i32, extent, keep_intermediates=False):
+        """Voxel scatter-mean, student, kNN, affinity softmax, pooling (models/affinity_module.py:1524-1589).
+        Returns (pooled [M,D] in sorted voxel order, p2v_sorted [N] int32)."""
+        d = self.feature_dim
+        m = voxel_coords_i32.shape[0]
+        index = ops.VoxelIndex(voxel_coords_i32, extent)
+        p2v_sorted = index.rank[p2v_i32.long()].contiguous()
+        plan = ops.ScatterPlan(p2v_sorted, m)
+        stride = self.affinity_student.input_stride
+        vin = torch.zeros((m, stride), dtype=torch.float32, device=lifted.device)
+        plan.mean(lifted, d, vin, 0)
+        plan.mean(gauss, 6, vin, d)
+        nbr27 = index.kernel_map()
+        embed = self.affinity_student.forward_sorted(vin, nbr27, normalize=True)
+        nbr_orig, nbr_sorted = index.knn(self.K, want_orig=keep_intermediates, want_sorted=True)
+        w = ops.affinity_softmax(embed, nbr_sorted, self.affinity_sharpen_factor)
+        pooled = ops.pool(vin, d, nbr_sorted, w, self.n_pool)
+        if keep_intermediates:
+            self.last = dict(index=index, voxel_in=vin, embed=embed, knn_orig=nbr_orig, knn_sorted=nbr_sorted,
+                             weights=w, pooled=pooled, p2v_sorted=p2v_sorted, nbr27=nbr27)
+        return pooled, p2v_sorted
+
+    @torch.no_grad()
+    def evaluate_scene(self, batch_data, vis_prefix="scene0695_00", keep_intermediates=False):
+        """Reference signature and return value (models/affinity_module.py:1490-1608)."""
+        f_full, text_features, logit_scale = self.lift_lseg_features(batch_data)
+        scene_coords_3d, inds = batch_data[1], batch_data[2]
+        gauss = batch_data[19][:, :6].float().cuda().contiguous()
+        vox = scene_coords_3d.to(torch.int32)
+        extent = tuple(int(e) + 1 for e in vox.max(0).values.tolist())
+        if keep_intermediates:
+            self.last_lifted = f_full
+        pooled, p2v_sorted = self.purify(f_full, gauss, vox.cuda().contiguous(), inds.to(torch.int32).cuda(), extent,
+                                         keep_intermediates)
+        scene_features = ops.gather_rows(pooled, self.feature_dim, p2v_sorted)
+        return {"scene_features": scene_features, "text_features": text_features, "logit_scale": logit_scale}
+
+    # ------------------------------------------------------------------ B200-first whole-scene path
+    @torch.no_grad()
+    def run_scene(self, s: SceneInputs, hist=None, ignore=None, keep_intermediates=False):
+        """Stages 1a-4 on the device: fused project + gather-mean, fill, purify, per-voxel classification,
+        label gather + IoU histograms.  Returns dict(labels_voxel, p2v_sorted, hist, seen)."""
+        W, H = s.image_dim
+        d = self.feature_dim
+        _, counts = ops.project_views(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres)
+        keep = ops.accept_views(counts, self.min_visible)
+        lifted, seen = ops.lift_mean_fused(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, keep, s.feat)
+        nn = ops.nn1_fill(s.coords_f32, seen, self.fill_cell)
+        ops.copy_rows(lifted, d, nn)
+        if keep_intermediates:
+            self.last_lifted, self.last_seen, self.last_keep, self.last_counts = lifted, seen, keep, counts
+        pooled, p2v_sorted = self.purify(lifted, s.gauss, s.voxel_coords, s.p2v, s.extent, keep_intermediates)
+        labels_vox, _, _ = ops.logits_argmax(pooled, d, self.text_features, self.logit_scale, want_zero=False)
+        out = dict(labels_voxel=labels_vox, p2v_sorted=p2v_sorted, seen=seen, pooled=pooled)
+        if s.labels is not None:
+            c = self.text_features.shape[0]
+            out["hist"], out["pred"] = ops.iou_hist(labels_vox, p2v_sorted, s.labels, ignore, c, hist,
+                                                    want_pred=keep_intermediates)
+        return out
+
+
+GeoPurifyB200 = SonataXAffinityTrainer
+
+
+def scene_inputs_from_synth(scene, feat_dtype=torch.bfloat16, device="cuda", coords_f64=True):
+    """Upload a `geopurify_b200.synth.Scene` (host numpy) to the device in the layout `run_scene` expects.
+    The dense feature map is the table lookup of the id map -- the stand-in for the 2-D VLM output."""
+    from .synth import mapper_intrinsics
+    dev = torch.device(device)
+    W, H = scene.image_dim
+    k = mapper_intrinsics(scene.intrinsics, scene.image_dim)
+    intr = np.array([k[0, 0], k[1, 1], k[0, 2], k[1, 2]], dtype=np.float64)
+    w2c, intr_d = ops.cameras_to_device(scene.w2c, intr)
+    c32 = torch.as_tensor(scene.coords).to(dev)
+    coords = c32.double() if coords_f64 else c32
+    tables = torch.as_tensor(scene.tables).to(dev).to(feat_dtype)
+    idm = torch.as_tensor(scene.idmaps).to(dev).long()
+    feat = torch.stack([tables[v][idm[v]] for v in range(scene.n_views)]).contiguous()
+    vox = torch.as_tensor(scene.voxel_coords.astype(np.int32)).to(dev)
+    extent = tuple(int(e) + 1 for e in scene.voxel_coords.max(0))
+    return SceneInputs(coords=coords.contiguous(), coords_f32=c32.contiguous(),
+                       gauss=torch.as_tensor(scene.gauss).to(dev).contiguous(), voxel_coords=vox.contiguous(),
+                       p2v=torch.as_tensor(scene.inds_reconstruct.astype(np.int32)).to(dev), extent=extent, w2c=w2c,
+                       intr=intr_d, depth=torch.as_tensor(scene.depth).to(dev).contiguous(), feat=feat,
+                       image_dim=(W, H), cut=scene.cut, vis_thres=scene.vis_thres,
+                       labels=torch.as_tensor(scene.labels).to(dev))

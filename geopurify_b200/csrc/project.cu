@@ -1,0 +1,430 @@
+// Stage 1: point -> view projection, occlusion test, z-buffer depth, fused gather-mean lifting.
+// Replaces PointCloudToImageMapper.compute_mapping (reference models/utils/fusion_util.py:99-147, :45-82)
+// and the gather + mean of lift_lseg_features (reference models/affinity_module.py:404-438).
+#include "common.cuh"
+
+#define GP_MAX_VIEWS_SMEM 256
+
+struct Cam {  // 20 doubles per view
+  double m[12];  // rows 0..2 of W2C
+  double fx, fy, cx, cy;
+};
+
+__device__ __forceinline__ void load_cams(Cam* s, const double* w2c, const double* intr, int v0, int nv) {
+  for (int i = threadIdx.x; i < nv * 20; i += blockDim.x) {
+    int v = i / 20, j = i % 20;
+    double val = j < 12 ? w2c[(size_t)(v0 + v) * 16 + j] : intr[(size_t)(v0 + v) * 4 + (j - 12)];
+    ((double*)s)[i] = val;
+  }
+}
+
+// numpy's 4x4 @ 4xN float64 product runs through OpenBLAS dgemm: an FMA chain over k = 0..3 starting from
+// a0*x (verified bit-for-bit against numpy); the rest is separate IEEE ops (numpy ufuncs).
+__device__ __forceinline__ bool project_point(const Cam& c, double x, double y, double z, int H, int W, int cut,
+                                              double& pz, int& row, int& col) {
+  double p0 = __fma_rn(c.m[3], 1.0, __fma_rn(c.m[2], z, __fma_rn(c.m[1], y, __dmul_rn(c.m[0], x))));
+  double p1 = __fma_rn(c.m[7], 1.0, __fma_rn(c.m[6], z, __fma_rn(c.m[5], y, __dmul_rn(c.m[4], x))));
+  double p2 = __fma_rn(c.m[11], 1.0, __fma_rn(c.m[10], z, __fma_rn(c.m[9], y, __dmul_rn(c.m[8], x))));
+  double u = __dadd_rn(__ddiv_rn(__dmul_rn(p0, c.fx), p2), c.cx);
+  double v = __dadd_rn(__ddiv_rn(__dmul_rn(p1, c.fy), p2), c.cy);
+  double ru = rint(u), rv = rint(v);  // np.round: half to even
+  pz = p2;
+  // NaN / inf / out-of-int64 values become INT64_MIN in numpy's astype(int) and fail `>= cut`; the double
+  // comparisons below reject exactly the same inputs.
+  bool inside = (ru >= (double)cut) && (rv >= (double)cut) && (ru < (double)(W - cut)) && (rv < (double)(H - cut));
+  if (inside) {
+    col = (int)ru;
+    row = (int)rv;
+  }
+  return inside;
+}
+
+template <int DEPTH_DTYPE>
+__device__ __forceinline__ bool depth_test(const void* depth, size_t off, double pz, double thr, float thr32) {
+  if (DEPTH_DTYPE == 0) return pz > 0.0;
+  if (DEPTH_DTYPE == GP_F64) {
+    double d = __ldg((const double*)depth + off);
+    return fabs(__dsub_rn(d, pz)) <= __dmul_rn(thr, d);
+  } else {
+    float d = __ldg((const float*)depth + off);
+    // numpy: float32 array * python float stays float32; float32 array - float64 array is float64
+    return fabs(__dsub_rn((double)d, pz)) <= (double)__fmul_rn(thr32, d);
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ void load_xyz(const void* coords, int64_t i, double& x, double& y, double& z) {
+  const T* c = (const T*)coords + 3 * i;
+  x = (double)c[0];
+  y = (double)c[1];
+  z = (double)c[2];
+}
+
+// ------------------------------------------------------------------ gp_project_views
+template <typename CT, int DEPTH_DTYPE>
+__global__ void __launch_bounds__(256) project_views_kernel(const void* __restrict__ coords, int64_t n,
+                                                             const double* __restrict__ w2c,
+                                                             const double* __restrict__ intr,
+                                                             const void* __restrict__ depth, int V, int H, int W,
+                                                             int cut, double thr, int32_t* __restrict__ pix,
+                                                             int32_t* __restrict__ counts) {
+  extern __shared__ double smem_d[];
+  Cam* cams = (Cam*)smem_d;
+  int* cnt = (int*)(cams + V);
+  load_cams(cams, w2c, intr, 0, V);
+  for (int i = threadIdx.x; i < V; i += blockDim.x) cnt[i] = 0;
+  __syncthreads();
+  const float thr32 = (float)thr;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool live = i < n;
+  double x = 0, y = 0, z = 0;
+  if (live) load_xyz<CT>(coords, i, x, y, z);
+  for (int v = 0; v < V; ++v) {
+    int row = 0, col = 0;
+    double pz;
+    bool vis = false;
+    if (live) {
+      vis = project_point(cams[v], x, y, z, H, W, cut, pz, row, col);
+      if (vis) vis = depth_test<DEPTH_DTYPE>(depth, ((size_t)v * H + row) * W + col, pz, thr, thr32);
+      pix[(size_t)v * n + i] = vis ? row * W + col : -1;
+    }
+    unsigned b = __ballot_sync(0xffffffffu, vis);
+    if ((threadIdx.x & 31) == 0 && b) atomicAdd(&cnt[v], __popc(b));
+  }
+  __syncthreads();
+  for (int v = threadIdx.x; v < V; v += blockDim.x)
+    if (cnt[v]) atomicAdd(&counts[v], cnt[v]);
+}
+
+extern "C" int gp_project_views(const void* coords, int coords_dtype, int64_t n, const double* w2c,
+                                const double* intr, const void* depth, int depth_dtype, int V, int H, int W,
+                                int cut, double vis_thres, int32_t* pix, int32_t* counts, gp_stream_t stream) {
+  GP_CHECK_ARG(n >= 0 && V >= 0 && H > 0 && W > 0 && cut >= 0, "gp_project_views: bad sizes");
+  GP_CHECK_ARG(V <= GP_MAX_VIEWS_SMEM, "gp_project_views: V=%d exceeds %d views per call", V, GP_MAX_VIEWS_SMEM);
+  GP_CHECK_ARG(coords_dtype == GP_F32 || coords_dtype == GP_F64, "gp_project_views: coords dtype");
+  GP_CHECK_ARG((depth == nullptr) == (depth_dtype == 0), "gp_project_views: depth pointer / dtype mismatch");
+  GP_CHECK_ARG(depth_dtype == 0 || depth_dtype == GP_F32 || depth_dtype == GP_F64, "gp_project_views: depth dtype");
+  GP_CHECK_ARG((int64_t)H * W < (1ll << 31), "gp_project_views: image too large");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (V == 0) return GP_OK;
+  GP_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * V, st));
+  if (n == 0) return GP_OK;
+  size_t smem = sizeof(Cam) * V + sizeof(int) * V;
+  unsigned grid = (unsigned)((n + 255) / 256);
+#define LAUNCH(CT, DD)                                                                                          \
+  project_views_kernel<CT, DD><<<grid, 256, smem, st>>>(coords, n, w2c, intr, depth, V, H, W, cut, vis_thres, \
+                                                        pix, counts)
+  if (coords_dtype == GP_F64) {
+    if (depth_dtype == 0) LAUNCH(double, 0);
+    else if (depth_dtype == GP_F64) LAUNCH(double, GP_F64);
+    else LAUNCH(double, GP_F32);
+  } else {
+    if (depth_dtype == 0) LAUNCH(float, 0);
+    else if (depth_dtype == GP_F64) LAUNCH(float, GP_F64);
+    else LAUNCH(float, GP_F32);
+  }
+#undef LAUNCH
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+// ------------------------------------------------------------------ gp_pix_to_mapping
+__global__ void pix_to_mapping_kernel(const int32_t* __restrict__ pix, int64_t total, int W,
+                                      int64_t* __restrict__ mapping) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  int p = pix[i];
+  int64_t r = 0, c = 0, m = 0;
+  if (p >= 0) {
+    r = p / W;
+    c = p % W;
+    m = 1;
+  }
+  mapping[3 * i] = r;
+  mapping[3 * i + 1] = c;
+  mapping[3 * i + 2] = m;
+}
+
+extern "C" int gp_pix_to_mapping(const int32_t* pix, int64_t total, int W, int64_t* mapping, gp_stream_t stream) {
+  GP_CHECK_ARG(total >= 0 && W > 0, "gp_pix_to_mapping: bad sizes");
+  if (total == 0) return GP_OK;
+  pix_to_mapping_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(pix, total, W, mapping);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+// ------------------------------------------------------------------ gp_splat_depth
+// Positive doubles order like their bit patterns, so the z-buffer min is an atomicMin on uint64.
+template <typename CT>
+__global__ void __launch_bounds__(256) splat_depth_kernel(const void* __restrict__ coords, int64_t n,
+                                                           const double* __restrict__ w2c,
+                                                           const double* __restrict__ intr, int V, int H, int W,
+                                                           int cut, unsigned long long* __restrict__ depth_bits) {
+  extern __shared__ double smem_d[];
+  Cam* cams = (Cam*)smem_d;
+  load_cams(cams, w2c, intr, 0, V);
+  __syncthreads();
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double x, y, z;
+  load_xyz<CT>(coords, i, x, y, z);
+  for (int v = 0; v < V; ++v) {
+    int row, col;
+    double pz;
+    if (project_point(cams[v], x, y, z, H, W, cut, pz, row, col) && pz > 0.2)
+      atomicMin(&depth_bits[((size_t)v * H + row) * W + col], (unsigned long long)__double_as_longlong(pz));
+  }
+}
+
+__global__ void fill_f64_kernel(double* p, int64_t n, double val) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = val;
+}
+
+extern "C" int gp_splat_depth(const void* coords, int coords_dtype, int64_t n, const double* w2c, const double* intr,
+                              int V, int H, int W, int cut, double* depth, gp_stream_t stream) {
+  GP_CHECK_ARG(n >= 0 && V >= 0 && H > 0 && W > 0 && cut >= 0, "gp_splat_depth: bad sizes");
+  GP_CHECK_ARG(V <= GP_MAX_VIEWS_SMEM, "gp_splat_depth: too many views");
+  GP_CHECK_ARG(coords_dtype == GP_F32 || coords_dtype == GP_F64, "gp_splat_depth: coords dtype");
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t total = (int64_t)V * H * W;
+  if (total == 0) return GP_OK;
+  fill_f64_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(depth, total, 999999.0);
+  GP_LAUNCH_CHECK();
+  if (n == 0) return GP_OK;
+  unsigned grid = (unsigned)((n + 255) / 256);
+  size_t smem = sizeof(Cam) * V;
+  if (coords_dtype == GP_F64)
+    splat_depth_kernel<double><<<grid, 256, smem, st>>>(coords, n, w2c, intr, V, H, W, cut,
+                                                        (unsigned long long*)depth);
+  else
+    splat_depth_kernel<float><<<grid, 256, smem, st>>>(coords, n, w2c, intr, V, H, W, cut,
+                                                       (unsigned long long*)depth);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+// ------------------------------------------------------------------ gp_accept_views
+__global__ void accept_views_kernel(const int32_t* counts, int V, int lo, int hi, uint8_t* keep) {
+  int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < V) {
+    int c = counts[v];
+    keep[v] = (c != 0 && c >= lo && c <= hi) ? 1 : 0;
+  }
+}
+
+extern "C" int gp_accept_views(const int32_t* counts, int V, int min_visible, int max_visible, uint8_t* keep,
+                               gp_stream_t stream) {
+  GP_CHECK_ARG(V >= 0, "gp_accept_views: bad V");
+  if (V == 0) return GP_OK;
+  accept_views_kernel<<<(V + 127) / 128, 128, 0, (cudaStream_t)stream>>>(counts, V, min_visible, max_visible, keep);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+// ------------------------------------------------------------------ fused lifting
+// One warp per point.  Lane l projects views l, l+32, ... (cameras in shared memory), the warp ballots the
+// visible set and then walks it in ascending view order, every lane pulling 128-bit pieces of the feature row.
+// NV4 = float4 accumulators per lane: D = 128 * NV4.
+template <int NV4, bool BF16>
+__device__ __forceinline__ void accumulate_row(const void* feat, size_t row_index, int D, int lane, float4 (&acc)[NV4]) {
+  if constexpr (!BF16) {
+    const float4* p = (const float4*)((const float*)feat + row_index * (size_t)D);
+    float4 t[NV4];
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) t[j] = ldg_stream_f4(p + j * 32 + lane);
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) {
+      acc[j].x = __fadd_rn(acc[j].x, t[j].x);
+      acc[j].y = __fadd_rn(acc[j].y, t[j].y);
+      acc[j].z = __fadd_rn(acc[j].z, t[j].z);
+      acc[j].w = __fadd_rn(acc[j].w, t[j].w);
+    }
+  } else {
+    // lane owns 8 consecutive bf16 per 256-element chunk -> two float4 accumulators per uint4
+    const uint4* p = (const uint4*)((const __nv_bfloat16*)feat + row_index * (size_t)D);
+    uint4 t[NV4 / 2 > 0 ? NV4 / 2 : 1];
+#pragma unroll
+    for (int j = 0; j < NV4 / 2; ++j) t[j] = ldg_stream_u4(p + j * 32 + lane);
+#pragma unroll
+    for (int j = 0; j < NV4 / 2; ++j) {
+      acc[2 * j].x = __fadd_rn(acc[2 * j].x, __uint_as_float(t[j].x << 16));
+      acc[2 * j].y = __fadd_rn(acc[2 * j].y, __uint_as_float(t[j].x & 0xffff0000u));
+      acc[2 * j].z = __fadd_rn(acc[2 * j].z, __uint_as_float(t[j].y << 16));
+      acc[2 * j].w = __fadd_rn(acc[2 * j].w, __uint_as_float(t[j].y & 0xffff0000u));
+      acc[2 * j + 1].x = __fadd_rn(acc[2 * j + 1].x, __uint_as_float(t[j].z << 16));
+      acc[2 * j + 1].y = __fadd_rn(acc[2 * j + 1].y, __uint_as_float(t[j].z & 0xffff0000u));
+      acc[2 * j + 1].z = __fadd_rn(acc[2 * j + 1].z, __uint_as_float(t[j].w << 16));
+      acc[2 * j + 1].w = __fadd_rn(acc[2 * j + 1].w, __uint_as_float(t[j].w & 0xffff0000u));
+    }
+  }
+}
+
+template <int NV4, bool BF16>
+__device__ __forceinline__ void store_mean(float* out, int64_t out_stride, int64_t i, int lane, float4 (&acc)[NV4],
+                                           int count) {
+  // reference: counter[counter == 0] = 1e-6; sum / counter (models/affinity_module.py:435-436)
+  float c = count ? (float)count : 1e-6f;
+  float* o = out + i * out_stride;
+  if constexpr (!BF16) {
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) {
+      float4 r = make_float4(__fdiv_rn(acc[j].x, c), __fdiv_rn(acc[j].y, c), __fdiv_rn(acc[j].z, c),
+                             __fdiv_rn(acc[j].w, c));
+      ((float4*)o)[j * 32 + lane] = r;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < NV4 / 2; ++j) {
+      float4 r0 = make_float4(__fdiv_rn(acc[2 * j].x, c), __fdiv_rn(acc[2 * j].y, c), __fdiv_rn(acc[2 * j].z, c),
+                              __fdiv_rn(acc[2 * j].w, c));
+      float4 r1 = make_float4(__fdiv_rn(acc[2 * j + 1].x, c), __fdiv_rn(acc[2 * j + 1].y, c),
+                              __fdiv_rn(acc[2 * j + 1].z, c), __fdiv_rn(acc[2 * j + 1].w, c));
+      ((float4*)o)[(j * 32 + lane) * 2] = r0;
+      ((float4*)o)[(j * 32 + lane) * 2 + 1] = r1;
+    }
+  }
+}
+
+template <typename CT, int DEPTH_DTYPE, int NV4, bool BF16, bool FROM_PIX>
+__global__ void __launch_bounds__(256) lift_mean_kernel(const void* __restrict__ coords, int64_t n,
+                                                         const double* __restrict__ w2c,
+                                                         const double* __restrict__ intr,
+                                                         const void* __restrict__ depth, int V, int H, int W, int cut,
+                                                         double thr, const uint8_t* __restrict__ keep,
+                                                         const int32_t* __restrict__ pix_in,
+                                                         const void* __restrict__ feat, int D, float* __restrict__ out,
+                                                         int64_t out_stride, uint8_t* __restrict__ seen) {
+  extern __shared__ double smem_d[];
+  Cam* cams = (Cam*)smem_d;
+  uint8_t* skeep = (uint8_t*)(cams + (FROM_PIX ? 0 : V));
+  if (!FROM_PIX) load_cams(cams, w2c, intr, 0, V);
+  for (int i = threadIdx.x; i < V; i += blockDim.x) skeep[i] = keep ? keep[i] : 1;
+  __syncthreads();
+  const float thr32 = (float)thr;
+  const int lane = threadIdx.x & 31;
+  const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const size_t hw = (size_t)H * W;
+  for (int64_t i = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < n; i += warps_total) {
+    double x = 0, y = 0, z = 0;
+    if (!FROM_PIX) load_xyz<CT>(coords, i, x, y, z);
+    float4 acc[NV4];
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    int count = 0;
+    for (int v0 = 0; v0 < V; v0 += 32) {
+      int v = v0 + lane;
+      int p = -1;
+      if (v < V && skeep[v]) {
+        if (FROM_PIX) {
+          p = __ldg(pix_in + (size_t)v * n + i);
+        } else {
+          int row, col;
+          double pz;
+          if (project_point(cams[v], x, y, z, H, W, cut, pz, row, col) &&
+              depth_test<DEPTH_DTYPE>(depth, (size_t)v * hw + (size_t)row * W + col, pz, thr, thr32))
+            p = row * W + col;
+        }
+      }
+      unsigned b = __ballot_sync(0xffffffffu, p >= 0);
+      count += __popc(b);
+      while (b) {
+        int src = __ffs(b) - 1;
+        b &= b - 1;
+        int pp = __shfl_sync(0xffffffffu, p, src);
+        accumulate_row<NV4, BF16>(feat, (size_t)(v0 + src) * hw + (size_t)pp, D, lane, acc);
+      }
+    }
+    store_mean<NV4, BF16>(out, out_stride, i, lane, acc, count);
+    if (lane == 0) seen[i] = count > 0;
+  }
+}
+
+template <typename CT, int DD, bool FROM_PIX>
+static int launch_lift(const void* coords, int64_t n, const double* w2c, const double* intr, const void* depth, int V,
+                       int H, int W, int cut, double thr, const uint8_t* keep, const int32_t* pix, const void* feat,
+                       int feat_dtype, int D, float* out, int64_t out_stride, uint8_t* seen, cudaStream_t st) {
+  size_t smem = (FROM_PIX ? 0 : sizeof(Cam) * V) + V;
+  int64_t warps = n;
+  int64_t blocks = (warps + 7) / 8;
+  int64_t cap = (int64_t)GP_SM_COUNT * 8 * 16;  // grid-stride beyond 16 waves of 8 CTAs/SM
+  unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
+  int nv4 = D / 128;
+#define LIFT(NV4, BF)                                                                                        \
+  lift_mean_kernel<CT, DD, NV4, BF, FROM_PIX><<<grid, 256, smem, st>>>(coords, n, w2c, intr, depth, V, H, W, \
+                                                                       cut, thr, keep, pix, feat, D, out,    \
+                                                                       out_stride, seen)
+  if (feat_dtype == GP_F32) {
+    switch (nv4) {
+      case 1: LIFT(1, false); break;
+      case 2: LIFT(2, false); break;
+      case 4: LIFT(4, false); break;
+      case 6: LIFT(6, false); break;
+      case 8: LIFT(8, false); break;
+      default: gp_set_error("lift: unsupported D=%d (fp32 needs D in {128,256,512,768,1024})", D); return GP_ERR_ARG;
+    }
+  } else {
+    switch (nv4) {
+      case 2: LIFT(2, true); break;
+      case 4: LIFT(4, true); break;
+      case 6: LIFT(6, true); break;
+      case 8: LIFT(8, true); break;
+      default: gp_set_error("lift: unsupported D=%d (bf16 needs D in {256,512,768,1024})", D); return GP_ERR_ARG;
+    }
+  }
+#undef LIFT
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    gp_set_error("lift kernel launch failed: %s", cudaGetErrorString(e));
+    return GP_ERR_CUDA;
+  }
+  return GP_OK;
+}
+
+static int check_lift_common(int64_t n, int V, int H, int W, int feat_dtype, int D, int64_t out_stride,
+                             const float* out) {
+  GP_CHECK_ARG(n >= 0 && V >= 0 && H > 0 && W > 0, "lift: bad sizes");
+  GP_CHECK_ARG(V <= GP_MAX_VIEWS_SMEM, "lift: too many views");
+  GP_CHECK_ARG(feat_dtype == GP_F32 || feat_dtype == GP_BF16, "lift: feature dtype must be f32 or bf16");
+  GP_CHECK_ARG(D > 0 && D % 128 == 0 && D <= 1024, "lift: D must be a multiple of 128, <= 1024");
+  GP_CHECK_ARG(out_stride >= D && out_stride % 4 == 0 && ((uintptr_t)out % 16) == 0,
+               "lift: out must be 16-byte aligned with stride %% 4 == 0");
+  return GP_OK;
+}
+
+extern "C" int gp_lift_mean_fused(const void* coords, int coords_dtype, int64_t n, const double* w2c,
+                                  const double* intr, const void* depth, int depth_dtype, int V, int H, int W,
+                                  int cut, double vis_thres, const uint8_t* keep, const void* feat, int feat_dtype,
+                                  int D, float* out, int64_t out_stride, uint8_t* seen, gp_stream_t stream) {
+  int rc = check_lift_common(n, V, H, W, feat_dtype, D, out_stride, out);
+  if (rc) return rc;
+  GP_CHECK_ARG(coords_dtype == GP_F32 || coords_dtype == GP_F64, "lift: coords dtype");
+  GP_CHECK_ARG((depth == nullptr) == (depth_dtype == 0), "lift: depth pointer / dtype mismatch");
+  if (n == 0) return GP_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+#define GO(CT, DD)                                                                                              \
+  return launch_lift<CT, DD, false>(coords, n, w2c, intr, depth, V, H, W, cut, vis_thres, keep, nullptr, feat, \
+                                    feat_dtype, D, out, out_stride, seen, st)
+  if (coords_dtype == GP_F64) {
+    if (depth_dtype == 0) GO(double, 0);
+    if (depth_dtype == GP_F64) GO(double, GP_F64);
+    if (depth_dtype == GP_F32) GO(double, GP_F32);
+  } else {
+    if (depth_dtype == 0) GO(float, 0);
+    if (depth_dtype == GP_F64) GO(float, GP_F64);
+    if (depth_dtype == GP_F32) GO(float, GP_F32);
+  }
+#undef GO
+  gp_set_error("lift: depth dtype");
+  return GP_ERR_ARG;
+}
+
+extern "C" int gp_lift_mean_pix(const int32_t* pix, int64_t n, int V, int H, int W, const uint8_t* keep,
+                                const void* feat, int feat_dtype, int D, float* out, int64_t out_stride,
+                                uint8_t* seen, gp_stream_t stream) {
+  int rc = check_lift_common(n, V, H, W, feat_dtype, D, out_stride, out);
+  if (rc) return rc;
+  if (n == 0) return GP_OK;
+  return launch_lift<float, 0, true>(nullptr, n, nullptr, nullptr, nullptr, V, H, W, 0, 0.0, keep, pix, feat,
+                                     feat_dtype, D, out, out_stride, seen, (cudaStream_t)stream);
+}

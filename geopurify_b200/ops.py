@@ -1,0 +1,233 @@
+"""Thin torch-tensor wrappers over the C ABI: allocate outputs / workspaces, pass pointers, raise on error.
+
+Every function enqueues on the current CUDA stream and returns device tensors.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+
+def _dev():
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _ws(nbytes):
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=_dev())
+
+
+def cameras_to_device(w2c, intr):
+    """w2c [V,4,4] (any float dtype, true world-to-camera), intr [V,4] or [4] (fx,fy,cx,cy) -> float64 device tensors."""
+    w = torch.as_tensor(np.asarray(w2c, dtype=np.float64).reshape(-1, 16)).to(_dev())
+    k = np.asarray(intr, dtype=np.float64)
+    if k.ndim == 1:
+        k = np.repeat(k[None, :], w.shape[0], 0)
+    return w.contiguous(), torch.as_tensor(np.ascontiguousarray(k)).to(_dev())
+
+
+def project_views(coords, w2c, intr, depth, H, W, cut, vis_thres):
+    """A1: returns pix [V,N] int32 (row*W+col or -1) and counts [V] int32."""
+    lib = L.load()
+    n, V = coords.shape[0], w2c.shape[0]
+    pix = torch.empty((V, n), dtype=torch.int32, device=_dev())
+    counts = torch.empty((V,), dtype=torch.int32, device=_dev())
+    dd = 0 if depth is None else L.dtype_code(depth)
+    L.check(lib.gp_project_views(L.ptr(coords), L.dtype_code(coords), n, L.ptr(w2c), L.ptr(intr), L.ptr(depth), dd, V,
+                                 H, W, cut, float(vis_thres), L.ptr(pix), L.ptr(counts), L.stream()))
+    L.count(1)
+    return pix, counts
+
+
+def pix_to_mapping(pix, W):
+    lib = L.load()
+    out = torch.empty(pix.shape + (3,), dtype=torch.int64, device=_dev())
+    L.check(lib.gp_pix_to_mapping(L.ptr(pix), pix.numel(), W, L.ptr(out), L.stream()))
+    L.count(1)
+    return out
+
+
+def splat_depth(coords, w2c, intr, H, W, cut):
+    lib = L.load()
+    V = w2c.shape[0]
+    depth = torch.empty((V, H, W), dtype=torch.float64, device=_dev())
+    L.check(lib.gp_splat_depth(L.ptr(coords), L.dtype_code(coords), coords.shape[0], L.ptr(w2c), L.ptr(intr), V, H, W,
+                               cut, L.ptr(depth), L.stream()))
+    L.count(2)
+    return depth
+
+
+def accept_views(counts, min_visible=400, max_visible=2**31 - 1):
+    lib = L.load()
+    keep = torch.empty((counts.shape[0],), dtype=torch.uint8, device=_dev())
+    L.check(lib.gp_accept_views(L.ptr(counts), counts.shape[0], int(min_visible), int(max_visible), L.ptr(keep),
+                                L.stream()))
+    L.count(1)
+    return keep
+
+
+def lift_mean_fused(coords, w2c, intr, depth, H, W, cut, vis_thres, keep, feat, out=None, out_stride=None):
+    """A1+A4 fused.  feat [V,H,W,D] fp32/bf16 channels-last.  Returns (out [N,stride] fp32, seen [N] uint8)."""
+    lib = L.load()
+    n, V, D = coords.shape[0], w2c.shape[0], feat.shape[-1]
+    if out is None:
+        out_stride = out_stride or D
+        out = torch.empty((n, out_stride), dtype=torch.float32, device=_dev())
+    seen = torch.empty((n,), dtype=torch.uint8, device=_dev())
+    dd = 0 if depth is None else L.dtype_code(depth)
+    L.check(lib.gp_lift_mean_fused(L.ptr(coords), L.dtype_code(coords), n, L.ptr(w2c), L.ptr(intr), L.ptr(depth), dd,
+                                   V, H, W, cut, float(vis_thres), L.ptr(keep), L.ptr(feat), L.dtype_code(feat), D,
+                                   L.ptr(out), out.stride(0), L.ptr(seen), L.stream()))
+    L.count(1)
+    return out, seen
+
+
+def lift_mean_pix(pix, keep, feat, H, W, out=None, out_stride=None):
+    lib = L.load()
+    V, n = pix.shape
+    D = feat.shape[-1]
+    if out is None:
+        out_stride = out_stride or D
+        out = torch.empty((n, out_stride), dtype=torch.float32, device=_dev())
+    seen = torch.empty((n,), dtype=torch.uint8, device=_dev())
+    L.check(lib.gp_lift_mean_pix(L.ptr(pix), n, V, H, W, L.ptr(keep), L.ptr(feat), L.dtype_code(feat), D, L.ptr(out),
+                                 out.stride(0), L.ptr(seen), L.stream()))
+    L.count(1)
+    return out, seen
+
+
+def nn1_fill(xyz, seen, cell=0.05):
+    """Nearest seen point of every unseen point: nn [N] int32 (nn[i]=i when seen)."""
+    lib = L.load()
+    n = xyz.shape[0]
+    nn = torch.empty((n,), dtype=torch.int32, device=_dev())
+    nb = lib.gp_nn1_fill_workspace_bytes(n)
+    ws = _ws(nb)
+    L.check(lib.gp_nn1_fill(L.ptr(xyz), n, L.ptr(seen), float(cell), L.ptr(nn), L.ptr(ws), nb, L.stream()))
+    L.count(8)
+    return nn
+
+
+def copy_rows(rows, D, nn):
+    lib = L.load()
+    L.check(lib.gp_copy_rows(L.ptr(rows), rows.shape[0], D, rows.stride(0), L.ptr(nn), L.stream()))
+    L.count(1)
+    return rows
+
+
+class VoxelIndex:
+    """Morton-sorted voxel order + cell lists (device workspace)."""
+
+    def __init__(self, vox_i32, extent=None):
+        lib = L.load()
+        self.m = vox_i32.shape[0]
+        if extent is None:
+            extent = (vox_i32.max(0).values + 1).tolist() if self.m else [1, 1, 1]
+        self.ex, self.ey, self.ez = (int(e) for e in extent)
+        nb = lib.gp_voxel_index_workspace_bytes(self.m, self.ex, self.ey, self.ez)
+        if nb == 0:
+            raise L.GeoPurifyError(f"voxel index: unsupported sizes m={self.m} extent={extent}")
+        self.nbytes = nb
+        self.ws = _ws(nb)
+        self.order = torch.empty((self.m,), dtype=torch.int32, device=_dev())
+        self.rank = torch.empty((self.m,), dtype=torch.int32, device=_dev())
+        L.check(lib.gp_voxel_index_build(L.ptr(vox_i32), self.m, self.ex, self.ey, self.ez, L.ptr(self.order),
+                                         L.ptr(self.rank), L.ptr(self.ws), nb, L.stream()))
+        L.count(8)
+
+    def kernel_map(self):
+        lib = L.load()
+        out = torch.empty((self.m, 27), dtype=torch.int32, device=_dev())
+        L.check(lib.gp_kernel_map(L.ptr(self.ws), self.m, self.ex, self.ey, self.ez, L.ptr(out), L.stream()))
+        L.count(1)
+        return out
+
+    def knn(self, k, want_orig=True, want_sorted=True):
+        lib = L.load()
+        no = torch.empty((self.m, k), dtype=torch.int32, device=_dev()) if want_orig else None
+        ns = torch.empty((self.m, k), dtype=torch.int32, device=_dev()) if want_sorted else None
+        L.check(lib.gp_knn_grid(L.ptr(self.ws), self.m, self.ex, self.ey, self.ez, k, L.ptr(no), L.ptr(ns), L.stream()))
+        L.count(1)
+        return no, ns
+
+
+class ScatterPlan:
+    """CSR of points per destination row, reused for every scatter_mean with the same index."""
+
+    def __init__(self, p2v_i32, m):
+        lib = L.load()
+        self.n, self.m = p2v_i32.shape[0], int(m)
+        nb = lib.gp_scatter_mean_workspace_bytes(self.n, self.m)
+        self.ws = _ws(nb)
+        L.check(lib.gp_scatter_mean_prepare(L.ptr(p2v_i32), self.n, self.m, L.ptr(self.ws), nb, L.stream()))
+        L.count(6)
+
+    def mean(self, src, D, out, col0=0):
+        lib = L.load()
+        L.check(lib.gp_scatter_mean(L.ptr(src), src.stride(0), D, L.ptr(self.ws), self.n, self.m, L.ptr(out),
+                                    out.stride(0), col0, L.stream()))
+        L.count(1)
+        return out
+
+
+def affinity_softmax(embed, nbr_sorted, sharpen=20.0):
+    lib = L.load()
+    m, k = nbr_sorted.shape
+    w = torch.empty((m, k), dtype=torch.float32, device=_dev())
+    L.check(lib.gp_affinity_softmax(L.ptr(embed), embed.shape[1], L.ptr(nbr_sorted), m, k, float(sharpen), L.ptr(w),
+                                    L.stream()))
+    L.count(1)
+    return w
+
+
+def pool(f0, D, nbr_sorted, weights, T):
+    """T applications of the affinity matrix; returns a [m,D] tensor (or f0 itself when T == 0)."""
+    lib = L.load()
+    m, k = nbr_sorted.shape
+    if T == 0:
+        return f0
+    a = torch.empty((m, D), dtype=torch.float32, device=_dev())
+    b = torch.empty((m, D), dtype=torch.float32, device=_dev()) if T > 1 else a
+    outp = ctypes.c_void_p()
+    L.check(lib.gp_pool(L.ptr(f0), f0.stride(0), D, L.ptr(nbr_sorted), L.ptr(weights), m, k, T, L.ptr(a), L.ptr(b),
+                        ctypes.byref(outp), L.stream()))
+    L.count(T)
+    return a if outp.value == a.data_ptr() else b
+
+
+def gather_rows(rows, D, index_i32):
+    lib = L.load()
+    n = index_i32.shape[0]
+    out = torch.empty((n, D), dtype=torch.float32, device=_dev())
+    L.check(lib.gp_gather_rows(L.ptr(rows), rows.stride(0), D, L.ptr(index_i32), n, L.ptr(out), L.stream()))
+    L.count(1)
+    return out
+
+
+def logits_argmax(feat, D, text, logit_scale, want_logits=False, want_zero=True):
+    lib = L.load()
+    rows, C = feat.shape[0], text.shape[0]
+    label = torch.empty((rows,), dtype=torch.int32, device=_dev())
+    zero = torch.empty((rows,), dtype=torch.uint8, device=_dev()) if want_zero else None
+    logits = torch.empty((rows, C), dtype=torch.float32, device=_dev()) if want_logits else None
+    nb = lib.gp_logits_workspace_bytes(C, D)
+    ws = _ws(nb)
+    L.check(lib.gp_logits_argmax(L.ptr(feat), feat.stride(0), D, rows, L.ptr(text), C, float(logit_scale), L.ptr(label),
+                                 L.ptr(zero), L.ptr(logits), L.ptr(ws), nb, L.stream()))
+    L.count(2)
+    return label, zero, logits
+
+
+def iou_hist(label_rows, index, target, ignore, C, hist=None, want_pred=False):
+    lib = L.load()
+    n = target.shape[0]
+    if hist is None:
+        hist = torch.zeros((3, C), dtype=torch.int64, device=_dev())
+    pred = torch.empty((n,), dtype=torch.int64, device=_dev()) if want_pred else None
+    L.check(lib.gp_iou_hist(L.ptr(label_rows), L.ptr(index), L.ptr(target), n, L.ptr(ignore), ignore.shape[0], C,
+                            L.ptr(pred), L.ptr(hist), L.stream()))
+    L.count(1)
+    return hist, pred

@@ -1,0 +1,93 @@
+"""Mirror of the reference's classification + metric code on the CUDA path.
+
+Reference: run/validation.py:413-439 (normalise, logits, argmax, zero-row label fill, IoU call) and
+:458-553 (running sums, mIoU / mAcc / allAcc); util/util.py:108-124 (AverageMeter), :160-177
+(intersectionAndUnionGPU).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from . import ops
+
+
+class AverageMeter:
+    def __init__(self):
+        self.reset()
+
+    def reset(self):
+        self.val = 0
+        self.avg = 0
+        self.sum = 0
+        self.count = 0
+
+    def update(self, val, n=1):
+        self.val = val
+        self.sum += val * n
+        self.count += n
+        self.avg = self.sum / self.count
+
+
+def intersectionAndUnionGPU(output, target, K, ignore_indexs=[255]):
+    """util/util.py:160-177: `output[target == ign] = ign` IN PLACE, then three K-bin histograms as float32
+    CUDA tensors (area_intersection, area_union, area_target)."""
+    L.require_cuda()
+    assert output.dim() in [1, 2, 3, 4]
+    assert output.shape == target.shape
+    out_flat = output.view(-1)
+    tgt = target.view(-1).to(torch.int64).cuda().contiguous()
+    lab = out_flat.to(torch.int32).cuda().contiguous()
+    ign = torch.as_tensor(list(ignore_indexs), dtype=torch.int64).cuda()
+    hist, pred = ops.iou_hist(lab, None, tgt, ign, K, want_pred=True)
+    out_flat.copy_(pred.to(out_flat.dtype).to(out_flat.device))
+    h = hist.to(torch.float32)
+    return h[0], h[1], h[2]
+
+
+@torch.no_grad()
+def classify_scene(scene_features, text_features, logit_scale, scene_coords=None, fill_cell=0.05):
+    """run/validation.py:413-432: returns `scene_pred_2d` [N] int64 on the device.  Rows whose normalised
+    features are all zero copy the label of the nearest non-zero row, measured on columns 1:4 of the [N,3]
+    coordinate array, i.e. on (y, z) only -- the reference's quirk, kept."""
+    d = scene_features.shape[1]
+    label, zero, _ = ops.logits_argmax(scene_features.contiguous(), d, text_features.float().cuda().contiguous(),
+                                       float(logit_scale), want_zero=True)
+    if scene_coords is not None and bool(zero.any()) and not bool(zero.all()):
+        yz = scene_coords.float().cuda().clone()
+        yz[:, 0] = 0.0
+        nn = ops.nn1_fill(yz.contiguous(), (1 - zero).to(torch.uint8), fill_cell)
+        label = label[nn.long()]
+    return label.long()
+
+
+def mean_iou(inter_sum, union_sum, target_sum):
+    """run/validation.py:513-523 on float32 numpy sums."""
+    i = np.asarray(inter_sum, dtype=np.float32)
+    u = np.asarray(union_sum, dtype=np.float32)
+    t = np.asarray(target_sum, dtype=np.float32)
+    iou_class = i / (u + 1e-10)
+    acc_class = i / (t + 1e-10)
+    return float(np.mean(iou_class)), float(np.mean(acc_class)), float(sum(i) / (sum(t) + 1e-10))
+
+
+@torch.no_grad()
+def validate(val_loader, model, test_classes, test_ignore_label, logger=None):
+    """Loop body of run/validation.py:376-553 (All-classes meters).  Returns (mIoU, mAcc, allAcc) and the
+    three float32 running sums."""
+    im, um, tm = AverageMeter(), AverageMeter(), AverageMeter()
+    for i, batch_data in enumerate(val_loader):
+        if batch_data is None:
+            continue
+        scene_coords, scene_label = batch_data[0], batch_data[3]
+        res = model.evaluate_scene(batch_data)
+        pred = classify_scene(res["scene_features"], res["text_features"], res["logit_scale"], scene_coords)
+        inter, union, tgt = intersectionAndUnionGPU(pred, scene_label.detach().cuda(), test_classes, test_ignore_label)
+        im.update(inter.cpu().numpy())
+        um.update(union.cpu().numpy())
+        tm.update(tgt.cpu().numpy())
+        if logger:
+            logger.info("Process: [{}/{}]".format(i, len(val_loader)))
+    miou, macc, allacc = mean_iou(im.sum, um.sum, tm.sum)
+    return (miou, macc, allacc), (im.sum, um.sum, tm.sum)

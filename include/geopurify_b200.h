@@ -1,0 +1,181 @@
+/* geopurify_b200 -- C ABI of libgeopurify_b200.so (sm_100a).
+ *
+ * Drop-in boundary for the inference hot path of tj12323/GeoPurify.  The reference
+ * has no FFI of its own: its hot path is Python calling numpy / torch / third-party CUDA libraries.
+ * Each entry point below replaces one of those call sites (cited as reference file:line) and is what
+ * a ctypes binding in the reference tree would load.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host; plain pointers and sizes only;
+ *   - the caller owns all buffers, outputs included; functions never allocate what they return;
+ *     scratch comes from a caller-provided workspace whose size a *_workspace_bytes() query returns;
+ *   - all work is enqueued on `stream` (a cudaStream_t) and is asynchronous w.r.t. the host;
+ *   - return value: 0 = ok, GP_ERR_* otherwise; gp_last_error() gives the text for this thread;
+ *   - no global state, re-entrant, one device per process.
+ */
+#ifndef GEOPURIFY_B200_H
+#define GEOPURIFY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* gp_stream_t; /* cudaStream_t */
+
+enum {
+  GP_OK = 0,
+  GP_ERR_ARG = 1,       /* bad argument (shape, alignment, unsupported size) */
+  GP_ERR_WORKSPACE = 2, /* workspace too small */
+  GP_ERR_CUDA = 3       /* CUDA runtime error, text in gp_last_error() */
+};
+
+enum { GP_F32 = 1, GP_F64 = 2, GP_BF16 = 3 };
+
+int gp_version(void);
+const char* gp_last_error(void);
+
+/* ---- A1 + A3: PointCloudToImageMapper.compute_mapping for every view of a scene in one launch
+ * (models/utils/fusion_util.py:99-147, Matterport twin :45-82; callers dataset/data_loader_ablation.py:242-253,
+ * dataset/data_loader_matterport.py:194-205).  float64 arithmetic in the reference's operation order.
+ *   coords      [n,3]  float32 or float64 (coords_dtype)
+ *   w2c         [V,16] float64 row-major world-to-camera (the float32 matrix promoted; NOT transposed)
+ *   intr        [V,4]  float64 fx, fy, cx, cy (after the mapper ctor's rescale)
+ *   depth       [V,H,W] float32/float64 metres, or NULL with depth_dtype 0 (then the p.z > 0 test applies)
+ *   pix  (out)  [V,n]  int32 row*W+col of a visible point, -1 otherwise
+ *   counts(out) [V]    int32 visible points per view (zeroed by the call) */
+int gp_project_views(const void* coords, int coords_dtype, int64_t n, const double* w2c, const double* intr,
+                     const void* depth, int depth_dtype, int V, int H, int W, int cut, double vis_thres,
+                     int32_t* pix, int32_t* counts, gp_stream_t stream);
+
+/* pix -> the reference's mapping[V,n,3] int64 (row, col, mask), zeros where invisible (fusion_util.py:142-144). */
+int gp_pix_to_mapping(const int32_t* pix, int64_t total, int W, int64_t* mapping, gp_stream_t stream);
+
+/* ---- A2: z-buffer depth synthesis, the string-depth branch (fusion_util.py:126-130).
+ *   depth (out) [V,H,W] float64: min p.z over points with p.z > 0.2 inside the cut bound, 999999 elsewhere */
+int gp_splat_depth(const void* coords, int coords_dtype, int64_t n, const double* w2c, const double* intr, int V,
+                   int H, int W, int cut, double* depth, gp_stream_t stream);
+
+/* ---- A3: keep[v] = counts[v] != 0 && counts[v] >= min_visible && counts[v] <= max_visible
+ * (dataset/data_loader_ablation.py:254-288). */
+int gp_accept_views(const int32_t* counts, int V, int min_visible, int max_visible, uint8_t* keep,
+                    gp_stream_t stream);
+
+/* ---- A1+A4 fused: project, occlusion-test and gather-mean in one pass (models/affinity_module.py:404-438).
+ * One warp per point; cameras in shared memory; 128-bit loads of channels-last feature rows; float32 sum in
+ * ascending view order (the reference's index_add_ order).
+ *   feat        [V,H,W,D] float32 or bf16 (feat_dtype), D % 128 == 0 (fp32) / D % 256 == 0 (bf16), D <= 1024
+ *   keep        [V] uint8 or NULL (all views kept)
+ *   out  (out)  [n, out_stride] float32 mean feature in columns [0,D); other columns untouched
+ *   seen (out)  [n] uint8, 1 if at least one kept view saw the point */
+int gp_lift_mean_fused(const void* coords, int coords_dtype, int64_t n, const double* w2c, const double* intr,
+                       const void* depth, int depth_dtype, int V, int H, int W, int cut, double vis_thres,
+                       const uint8_t* keep, const void* feat, int feat_dtype, int D, float* out,
+                       int64_t out_stride, uint8_t* seen, gp_stream_t stream);
+
+/* ---- A4 from precomputed pixels (the reference's x_label / y_label / mask_2d form): same gather-mean, pix from
+ * gp_project_views or from the reference data loader. */
+int gp_lift_mean_pix(const int32_t* pix, int64_t n, int V, int H, int W, const uint8_t* keep, const void* feat,
+                     int feat_dtype, int D, float* out, int64_t out_stride, uint8_t* seen, gp_stream_t stream);
+
+/* ---- hole fill: 1-NN over float xyz (sklearn KDTree k=1 at models/affinity_module.py:445-449, 693-696;
+ * run/validation.py:425-430).  For every point with seen==0 finds the nearest seen point (float64 distance on
+ * the float32 coordinates, ties -> lowest index) and writes nn[i] = that index; nn[i] = i for seen points,
+ * -1 everywhere if no point is seen.  `cell` is the search-grid cell size in coordinate units. */
+size_t gp_nn1_fill_workspace_bytes(int64_t n);
+int gp_nn1_fill(const float* xyz, int64_t n, const uint8_t* seen, float cell, int32_t* nn, void* workspace,
+                size_t workspace_bytes, gp_stream_t stream);
+/* rows[i, 0:D) = rows[nn[i], 0:D) for nn[i] != i (out-of-place safe: sources are seen rows, never rewritten). */
+int gp_copy_rows(float* rows, int64_t n, int D, int64_t stride, const int32_t* nn, gp_stream_t stream);
+
+/* ---- voxel index: Morton-sorted order + cell lists over integer voxel coordinates (replaces the MinkowskiEngine
+ * coordinate map of models/affinity_module.py:1541-1545 and the faiss index of :1553-1554).
+ *   vox         [m,3] int32 non-negative voxel coordinates, unique rows
+ *   order (out) [m] int32  sorted position -> original voxel
+ *   rank  (out) [m] int32  original voxel -> sorted position
+ * (ex,ey,ez) = exclusive upper bound of the coordinates (<= 32768 each).  The built index lives in `workspace`
+ * and is consumed by gp_kernel_map / gp_knn_grid, which must be given the same (m, ex, ey, ez). */
+size_t gp_voxel_index_workspace_bytes(int64_t m, int ex, int ey, int ez);
+int gp_voxel_index_build(const int32_t* vox, int64_t m, int ex, int ey, int ez, int32_t* order, int32_t* rank,
+                         void* workspace, size_t workspace_bytes, gp_stream_t stream);
+
+/* ---- A7: 3^3 kernel map in SORTED space: nbr27[s, o] = sorted position of the voxel at coord(s) + delta_o,
+ * o = (dx+1) + 3(dy+1) + 9(dz+1), or -1. */
+int gp_kernel_map(const void* index_workspace, int64_t m, int ex, int ey, int ez, int32_t* nbr27,
+                  gp_stream_t stream);
+
+/* ---- A9: exact K nearest voxels, ascending (d^2, original index), self dropped, K <= 128
+ * (faiss IndexFlatL2 search at models/affinity_module.py:1553-1557).
+ *   nbr_orig   (out, may be NULL) [m,K] int32 rows/entries in ORIGINAL voxel numbering (the reference's
+ *                                  neighbor_indices)
+ *   nbr_sorted (out, may be NULL) [m,K] int32 rows/entries in SORTED numbering (input of gp_affinity / gp_pool) */
+int gp_knn_grid(const void* index_workspace, int64_t m, int ex, int ey, int ez, int K, int32_t* nbr_orig,
+                int32_t* nbr_sorted, gp_stream_t stream);
+
+/* ---- A6: torch_scatter.scatter_mean (models/affinity_module.py:1524-1535), deterministic: float32 sum in
+ * ascending point order, divided by the count.
+ *   src  [n, src_stride] float32, D columns used;  p2v [n] int32 point -> destination row (already composed
+ *   with `rank` when rows are wanted in sorted order);  out [m, out_stride], columns [col0, col0+D) written */
+size_t gp_scatter_mean_workspace_bytes(int64_t n, int64_t m);
+int gp_scatter_mean_prepare(const int32_t* p2v, int64_t n, int64_t m, void* workspace, size_t workspace_bytes,
+                            gp_stream_t stream);
+int gp_scatter_mean(const float* src, int64_t src_stride, int D, const void* prepared_workspace, int64_t n,
+                    int64_t m, float* out, int64_t out_stride, int col0, gp_stream_t stream);
+
+/* ---- A8: AffinityPredictor.forward + F.normalize (models/affinity_module.py:33-72, 1546-1547).
+ * Sparse 3^3 convolutions as gather-GEMM over the kernel map, BN (eval) + ReLU + residual epilogues.
+ *   x        [m, cin_stride] float32 rows in sorted order, cin columns valid
+ *   weights  packed by gp_student_pack_bytes()/the Python shim: per layer [kv, cin_pad, cout] float32,
+ *            then folded BN scale/shift [cout] pairs (see geopurify_b200/student.py)
+ *   embed (out) [m, E] float32 unit rows */
+typedef struct {
+  int n_layers;          /* conv layers, <= 16 */
+  int kv[16];            /* 27 or 1 */
+  int cin[16];           /* padded to a multiple of 32 */
+  int cout[16];
+  int bn[16];            /* 1: y = y*scale + shift */
+  int relu[16];          /* 1: ReLU after (BN, residual add) */
+  int residual_from[16]; /* -1, or index of the layer whose OUTPUT is added before the ReLU (-2: network input) */
+  int64_t w_off[16];     /* float offset of the layer's weights inside `weights` */
+  int64_t bn_off[16];    /* float offset of scale[cout] followed by shift[cout] */
+} gp_student_desc;
+size_t gp_student_workspace_bytes(const gp_student_desc* desc_host, int64_t m);
+int gp_student_forward(const gp_student_desc* desc_host, const float* weights, const float* x, int64_t cin_stride,
+                       const int32_t* nbr27, int64_t m, float* embed, int normalize, void* workspace,
+                       size_t workspace_bytes, gp_stream_t stream);
+
+/* ---- A10: w[s,k] = softmax_k(sharpen * <e_s, e_nbr(s,k)>) (models/affinity_module.py:1559-1572). */
+int gp_affinity_softmax(const float* embed, int E, const int32_t* nbr_sorted, int64_t m, int K, float sharpen,
+                        float* weights, gp_stream_t stream);
+
+/* ---- A11: F <- A F, T times (models/affinity_module.py:1575-1587); float32 accumulate.
+ *   f0 [m, stride] float32 (D columns pooled), buf_a/buf_b [m, D] ping-pong; result pointer returned in *out */
+int gp_pool(const float* f0, int64_t stride, int D, const int32_t* nbr_sorted, const float* weights, int64_t m,
+            int K, int T, float* buf_a, float* buf_b, float** out_host, gp_stream_t stream);
+
+/* ---- A11 tail: scene_features[n, 0:D) = pooled[rank[p2v_orig[n]], 0:D) (models/affinity_module.py:1589). */
+int gp_gather_rows(const float* rows, int64_t row_stride, int D, const int32_t* index, int64_t n, float* out,
+                   gp_stream_t stream);
+
+/* ---- A12: normalise, logits = s * f t^T, argmax (run/validation.py:413-417).
+ *   feat [rows, stride] float32 (D columns), text [C,D] float32 (raw; normalised inside)
+ *   label (out) [rows] int32 lowest-index argmax;  zero (out, may be NULL) [rows] uint8 1 if sum|f^| == 0 */
+size_t gp_logits_workspace_bytes(int C, int D);
+int gp_logits_argmax(const float* feat, int64_t stride, int D, int64_t rows, const float* text, int C,
+                     float logit_scale, int32_t* label, uint8_t* zero, float* logits_or_null, void* workspace,
+                     size_t workspace_bytes, gp_stream_t stream);
+
+/* ---- A12: intersectionAndUnionGPU (util/util.py:160-177): pred[target in ignore] = ignore, three histograms.
+ *   label_rows [rows] int32, index [n] int32 or NULL (pred[i] = label_rows[index[i]] else label_rows[i])
+ *   target [n] int64, ignore [n_ignore] int64 (device)
+ *   pred_out (may be NULL) [n] int64 prediction after the ignore overwrite
+ *   hist (out) [3,C] int64 intersection, union, target; ACCUMULATED into (caller zeroes once per run) */
+int gp_iou_hist(const int32_t* label_rows, const int32_t* index, const int64_t* target, int64_t n,
+                const int64_t* ignore, int n_ignore, int C, int64_t* pred_out, int64_t* hist, gp_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

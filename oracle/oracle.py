@@ -52,7 +52,7 @@ def project_view(world_to_camera_T, coords, depth, intrinsic, image_dim, vis_thr
     mapping = np.zeros((3, n), dtype=int)
     coords_new = np.concatenate([coords, np.ones([n, 1])], axis=1).T          # :111
     p = np.matmul(world_to_camera_T.T, coords_new)                            # :114
-    with np.errstate(divide="ignore", invalid="ignore"):
+    with np.errstate(all="ignore"):
         p[0] = (p[0] * intrinsic[0][0]) / p[2] + intrinsic[0][2]              # :115
         p[1] = (p[1] * intrinsic[1][1]) / p[2] + intrinsic[1][2]              # :116
         pi = np.round(p).astype(int)                                          # :117
@@ -81,7 +81,7 @@ def project_view_matterport(camera_to_world, coords, depth, intrinsic, image_dim
     coords_new = np.concatenate([coords, np.ones([n, 1])], axis=1).T
     world_to_camera = np.linalg.inv(camera_to_world)                          # :60
     p = np.matmul(world_to_camera, coords_new)
-    with np.errstate(divide="ignore", invalid="ignore"):
+    with np.errstate(all="ignore"):
         p[0] = (p[0] * intrinsic[0][0]) / p[2] + intrinsic[0][2]
         p[1] = (p[1] * intrinsic[1][1]) / p[2] + intrinsic[1][2]
         pi = np.round(p).astype(int)

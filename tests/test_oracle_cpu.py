@@ -1,0 +1,146 @@
+"""CPU suite: the oracle against the reference-generated golden vectors, oracle self-consistency, host logic."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from geopurify_b200 import synth
+from oracle import oracle
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, f"project_{name}.npz"))
+
+
+@pytest.mark.parametrize("name", ["scannet_f64", "scannet_f32depth"])
+def test_oracle_projection_matches_reference_golden(golden_dir, name):
+    g = _load(golden_dir, name)
+    W, H = g["image_dim"]
+    k = oracle.mapper_intrinsics(g["intrinsics"], (W, H))
+    for v in range(g["w2c_T"].shape[0]):
+        m, _ = oracle.project_view(g["w2c_T"][v], g["coords"], g["depth"][v], k, (W, H), float(g["vis_thres"]),
+                                   int(g["cut"]))
+        assert (m == g["mapping"][v]).all()
+    assert g["mapping"][..., 2].sum() > 100
+
+
+def test_oracle_projection_nodepth_and_splat(golden_dir):
+    g = _load(golden_dir, "scannet_nodepth_f32coords")
+    W, H = g["image_dim"]
+    k = oracle.mapper_intrinsics(g["intrinsics"], (W, H))
+    for v in range(g["w2c_T"].shape[0]):
+        m, _ = oracle.project_view(g["w2c_T"][v], g["coords"], None, k, (W, H), float(g["vis_thres"]), int(g["cut"]))
+        assert (m == g["mapping"][v]).all()
+    g = _load(golden_dir, "scannet_splat")
+    for v in range(g["w2c_T"].shape[0]):
+        m, _ = oracle.project_view(g["w2c_T"][v], g["coords"], None, k, (W, H), float(g["vis_thres"]), int(g["cut"]),
+                                   splat=True)
+        assert (m == g["mapping"][v]).all()
+
+
+def test_oracle_projection_edge_cases(golden_dir):
+    g = _load(golden_dir, "edge")
+    W, H = g["image_dim"]
+    k = oracle.mapper_intrinsics(g["intrinsics"], (W, H))
+    m, _ = oracle.project_view(g["w2c_T"][0], g["coords"], g["depth"][0], k, (W, H), float(g["vis_thres"]), 0)
+    assert (m == g["mapping"][0]).all()
+    m, _ = oracle.project_view(g["w2c_T"][0], g["coords"], None, k, (W, H), float(g["vis_thres"]), 0)
+    assert (m == g["mapping_nodepth"][0]).all()
+
+
+def test_oracle_projection_matterport(golden_dir):
+    g = _load(golden_dir, "matterport")
+    W, H = g["image_dim"]
+    for v in range(g["c2w"].shape[0]):
+        m = oracle.project_view_matterport(g["c2w"][v], g["coords"], g["depth"][v], g["intrinsics"], (W, H),
+                                           float(g["vis_thres"]), int(g["cut"]))
+        assert (m == g["mapping"][v]).all()
+
+
+def test_fnv_voxelizer_properties():
+    rng = np.random.default_rng(0)
+    pts = rng.uniform(0, 1, (5000, 3))
+    vox, inds, inv = synth.voxelize(pts, 0.05)
+    assert len(np.unique(vox, axis=0)) == len(vox)            # unique voxels
+    assert (vox[inv] == np.floor(np.floor(pts / 0.05) - np.floor(pts / 0.05).min(0))).all()
+    key = synth.fnv_hash_vec(vox)
+    assert (key[1:] > key[:-1]).all()                         # np.unique order = ascending key
+    # known-answer: FNV-1 style multiply-then-xor of (1,2,3)
+    h = 14695981039346656037
+    for c in (1, 2, 3):
+        h = ((h * 1099511628211) & (2**64 - 1)) ^ c
+    assert int(synth.fnv_hash_vec(np.array([[1, 2, 3]]))[0]) == h
+
+
+def test_knn_c_matches_numpy_and_tie_rule():
+    rng = np.random.default_rng(1)
+    c = np.unique(rng.integers(0, 12, (900, 3)), axis=0)
+    a = oracle.knn(c, 16)
+    b = oracle.knn_c(c, 16)
+    assert (a == b).all()
+    # contract: ascending (d2, index), self dropped
+    d2 = ((c[:, None] - c[None]) ** 2).sum(-1)
+    for i in (0, 5, len(c) - 1):
+        key = d2[i] * len(c) + np.arange(len(c))
+        exp = np.argsort(key)[1:17]
+        assert (a[i] == exp).all()
+    with pytest.raises(AssertionError):
+        oracle.knn(c[:10], 16)
+
+
+def test_kernel_map_variants_agree():
+    rng = np.random.default_rng(2)
+    c = np.unique(rng.integers(0, 9, (400, 3)), axis=0)
+    assert (oracle.kernel_map(c) == oracle.kernel_map_fast(c)).all()
+    nb = oracle.kernel_map_fast(c)
+    assert (nb[:, 13] == np.arange(len(c))).all()
+
+
+def test_pool_rows_are_convex_combinations():
+    rng = np.random.default_rng(3)
+    m, k = 300, 8
+    e = torch.nn.functional.normalize(torch.randn(m, 16), dim=1)
+    nbr = np.stack([rng.choice(m, k, replace=False) for _ in range(m)])
+    w = oracle.affinity_weights(e, nbr, 20.0)
+    assert torch.allclose(w.sum(1), torch.ones(m), atol=1e-5)
+    f = torch.rand(m, 12)
+    out = oracle.pool(f, nbr, w, 3)
+    assert out.min() >= f.min() - 1e-5 and out.max() <= f.max() + 1e-5
+    # linearity of the pooling operator
+    out2 = oracle.pool(2 * f + 1, nbr, w, 3)
+    assert torch.allclose(out2, 2 * out + 1, atol=1e-4)
+
+
+def test_iou_histograms_match_histc_and_numpy():
+    rng = np.random.default_rng(4)
+    k = 19
+    tgt = torch.as_tensor(rng.integers(0, 21, 5000))
+    out = torch.as_tensor(rng.integers(0, 19, 5000))
+    i, u, t = oracle.intersection_and_union(out, tgt, k, (19, 20))
+    o2 = out.numpy().copy()
+    o2[np.isin(tgt.numpy(), (19, 20))] = 255
+    inter = np.bincount(o2[o2 == tgt.numpy()], minlength=k)[:k]
+    ao = np.bincount(o2[o2 < k], minlength=k)[:k]
+    at = np.bincount(tgt.numpy()[tgt.numpy() < k], minlength=k)[:k]
+    assert (i.numpy() == inter).all() and (t.numpy() == at).all() and (u.numpy() == ao + at - inter).all()
+
+
+def test_oracle_whole_scene_runs(small_scene, small_state):
+    r = oracle.evaluate_scene(small_scene, small_state, k=16, n_iter=3, min_visible=50)
+    n, m = small_scene.n_points, small_scene.voxel_coords.shape[0]
+    assert r["scene_features"].shape == (n, 128) and r["knn"].shape == (m, 16)
+    assert torch.isfinite(r["scene_features"]).all()
+    assert float(r["seen"].float().mean()) > 0.1
+    miou, macc, allacc = oracle.miou(r["inter"].numpy(), r["union"].numpy(), r["target"].numpy())
+    assert 0.0 < miou <= 1.0
+
+
+def test_view_acceptance_renumbers():
+    maps = np.zeros((3, 10, 3), dtype=int)
+    maps[0, :5] = [3, 4, 1]
+    maps[2, 2:9] = [5, 6, 1]
+    kept, rows, cols, pids = oracle.accept_views(maps, min_visible=5)
+    assert kept == [0, 2] and list(pids[1]) == list(range(2, 9)) and (rows[0] == 3).all()
+    kept, *_ = oracle.accept_views(maps, min_visible=6)
+    assert kept == [2]
