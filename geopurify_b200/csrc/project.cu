@@ -5,14 +5,16 @@
 
 #define GP_MAX_VIEWS_SMEM 256
 
-struct Cam {  // 20 doubles per view
+struct Cam {  // 16 doubles per view
   double m[12];  // rows 0..2 of W2C
   double fx, fy, cx, cy;
 };
 
+static_assert(sizeof(Cam) == 128, "Cam is 16 doubles");
+
 __device__ __forceinline__ void load_cams(Cam* s, const double* w2c, const double* intr, int v0, int nv) {
-  for (int i = threadIdx.x; i < nv * 20; i += blockDim.x) {
-    int v = i / 20, j = i % 20;
+  for (int i = threadIdx.x; i < nv * 16; i += blockDim.x) {
+    int v = i >> 4, j = i & 15;
     double val = j < 12 ? w2c[(size_t)(v0 + v) * 16 + j] : intr[(size_t)(v0 + v) * 4 + (j - 12)];
     ((double*)s)[i] = val;
   }

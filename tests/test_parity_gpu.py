@@ -1,0 +1,233 @@
+"""GPU parity suite: every C-ABI entry point against the CPU oracle / the reference-generated golden vectors.
+
+Bit-exact: visibility masks, pixel rows/cols, z-buffer depth, kernel map, kNN indices, histograms.
+fp32 within the stated tolerance: lifted means (exact), scatter means (exact), student embeddings (2e-4),
+softmax weights (1e-4), pooled features (max-abs 1e-3, the north star's bound), labels (exact wherever the fp64
+top-2 margin exceeds 1e-4 of the logit scale).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from geopurify_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gp():
+    from geopurify_b200 import _lib, ops
+    _lib.require_cuda()
+    return ops
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, f"project_{name}.npz"))
+
+
+# ----------------------------------------------------------------------------- A1 / A2 vs the reference's outputs
+@pytest.mark.parametrize("name", ["scannet_f64", "scannet_f32depth", "scannet_nodepth_f32coords", "scannet_splat"])
+def test_mapper_matches_reference_golden(gp, golden_dir, name):
+    from geopurify_b200.fusion_util import PointCloudToImageMapper
+    g = _load(golden_dir, name)
+    W, H = (int(x) for x in g["image_dim"])
+    mapper = PointCloudToImageMapper([W, H], float(g["vis_thres"]), int(g["cut"]), g["intrinsics"])
+    for v in range(g["w2c_T"].shape[0]):
+        depth = "splat" if name == "scannet_splat" else (g["depth"][v] if "depth" in g.files else None)
+        m, w = mapper.compute_mapping(g["w2c_T"][v], g["coords"], depth)
+        assert m.shape == g["mapping"][v].shape and m.dtype.kind == "i"
+        assert (m == g["mapping"][v]).all(), f"{name} view {v}: {(m != g['mapping'][v]).any(1).sum()} rows differ"
+        if "weight" in g.files:
+            assert np.allclose(w, g["weight"][v], rtol=0, atol=0, equal_nan=True)
+
+
+def test_mapper_batched_views_match_golden(gp, golden_dir):
+    from geopurify_b200.fusion_util import PointCloudToImageMapper
+    g = _load(golden_dir, "scannet_f64")
+    W, H = (int(x) for x in g["image_dim"])
+    mapper = PointCloudToImageMapper([W, H], float(g["vis_thres"]), int(g["cut"]), g["intrinsics"])
+    pix, counts = mapper.compute_mapping_views(g["w2c_T"], g["coords"], g["depth"])
+    m = gp.pix_to_mapping(pix, W).cpu().numpy()
+    assert (m == g["mapping"]).all()
+    assert (counts.cpu().numpy() == g["mapping"][..., 2].sum(1)).all()
+
+
+def test_mapper_edge_cases(gp, golden_dir):
+    from geopurify_b200.fusion_util import PointCloudToImageMapper
+    g = _load(golden_dir, "edge")
+    W, H = (int(x) for x in g["image_dim"])
+    mapper = PointCloudToImageMapper([W, H], float(g["vis_thres"]), 0, g["intrinsics"])
+    m, _ = mapper.compute_mapping(g["w2c_T"][0], g["coords"], g["depth"][0])
+    assert (m == g["mapping"][0]).all()
+    m, _ = mapper.compute_mapping(g["w2c_T"][0], g["coords"], None)
+    assert (m == g["mapping_nodepth"][0]).all()
+
+
+def test_mapper_matterport(gp, golden_dir):
+    from geopurify_b200.fusion_util import PointCloudToImageMappermatterport
+    g = _load(golden_dir, "matterport")
+    W, H = (int(x) for x in g["image_dim"])
+    mapper = PointCloudToImageMappermatterport([W, H], float(g["vis_thres"]), int(g["cut"]))
+    for v in range(g["c2w"].shape[0]):
+        m = mapper.compute_mapping(g["c2w"][v], g["coords"], g["depth"][v], g["intrinsics"])
+        assert (m == g["mapping"][v]).all()
+
+
+def test_mapper_empty_and_shape_error(gp):
+    from geopurify_b200.fusion_util import PointCloudToImageMapper
+    mapper = PointCloudToImageMapper([320, 240], 0.05, 10, synth.scannet_intrinsics())
+    m, w = mapper.compute_mapping(np.eye(4, dtype=np.float32), np.zeros((0, 3)), None)
+    assert m.shape == (0, 3) and w.shape == (0,)
+    with pytest.raises(AssertionError):
+        mapper.compute_mapping(np.eye(4, dtype=np.float32), np.zeros((5, 2)), None)
+
+
+def test_splat_depth_matches_oracle(gp, small_scene):
+    from oracle import oracle
+    sc = small_scene
+    W, H = sc.image_dim
+    k = oracle.mapper_intrinsics(sc.intrinsics, sc.image_dim)
+    w2c, intr = gp.cameras_to_device(sc.w2c, [k[0, 0], k[1, 1], k[0, 2], k[1, 2]])
+    c = torch.as_tensor(sc.coords.astype(np.float64)).cuda()
+    d = gp.splat_depth(c, w2c, intr, H, W, sc.cut).cpu().numpy()
+    for v in range(sc.n_views):
+        _, dref = oracle.project_view(sc.w2c[v].T.copy(), sc.coords.astype(np.float64), None, k, (W, H), sc.vis_thres,
+                                      sc.cut, splat=True)
+        assert (d[v] == dref).all()
+
+
+# ----------------------------------------------------------------------------- whole-scene intermediates
+@pytest.fixture(scope="module")
+def scene_run(gp, small_scene, small_state):
+    """One small scene through the CUDA path (keep_intermediates) and through the oracle."""
+    from geopurify_b200.affinity_module import SonataXAffinityTrainer, scene_inputs_from_synth
+    from geopurify_b200.student import AffinityPredictor, load_numpy_state
+    from oracle import oracle
+    sc = small_scene
+    student = load_numpy_state(AffinityPredictor(134, 128, 128), small_state)
+    model = SonataXAffinityTrainer(text_features=sc.text, logit_scale=sc.logit_scale, student=student,
+                                   feature_dim=128, K=16, n_pool=3, min_visible=50)
+    s = scene_inputs_from_synth(sc, feat_dtype=torch.float32)
+    ign = torch.tensor([sc.ignore_label], dtype=torch.int64, device="cuda")
+    out = model.run_scene(s, ignore=ign, keep_intermediates=True)
+    torch.cuda.synchronize()
+    ref = oracle.evaluate_scene(sc, small_state, k=16, n_iter=3, min_visible=50)
+    return dict(sc=sc, model=model, s=s, out=out, ref=ref)
+
+
+def test_scene_projection_and_view_acceptance(gp, scene_run):
+    sc, model, s, ref = scene_run["sc"], scene_run["model"], scene_run["s"], scene_run["ref"]
+    W, H = sc.image_dim
+    pix, counts = gp.project_views(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres)
+    m = gp.pix_to_mapping(pix, W).cpu().numpy()
+    assert (m == ref["mappings"]).all()
+    keep = model.last_keep.cpu().numpy().astype(bool)
+    assert list(np.nonzero(keep)[0]) == list(ref["kept"])
+
+
+def test_scene_lift_mean_is_bit_exact(scene_run):
+    model, ref = scene_run["model"], scene_run["ref"]
+    lifted = model.last_lifted.cpu()
+    seen = model.last_seen.cpu().bool()
+    assert (seen == ref["seen"]).all()
+    assert torch.equal(lifted[seen], ref["lifted"][seen]), "seen rows: fp32 sum in view order must be bit-exact"
+    # filled rows copy the nearest seen row (KD-tree, exact distances): identical unless two seen points tie
+    diff = (lifted[~seen] != ref["lifted"][~seen]).any(1).sum().item()
+    assert diff == 0, f"{diff} filled rows differ"
+
+
+def test_scene_lift_from_pixels_equals_fused(gp, scene_run):
+    sc, model, s = scene_run["sc"], scene_run["model"], scene_run["s"]
+    W, H = sc.image_dim
+    pix, _ = gp.project_views(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres)
+    a, sa = gp.lift_mean_pix(pix, model.last_keep, s.feat, H, W)
+    b, sb = gp.lift_mean_fused(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, model.last_keep, s.feat)
+    assert torch.equal(a, b) and torch.equal(sa, sb)
+
+
+def test_scene_lift_bf16_maps(gp, scene_run):
+    """bf16 feature maps: the kernel must equal the fp32 path run on the bf16-rounded maps."""
+    sc, model, s = scene_run["sc"], scene_run["model"], scene_run["s"]
+    W, H = sc.image_dim
+    d = s.feat.shape[-1]
+    feat = torch.cat([s.feat, s.feat], -1) if d % 256 else s.feat     # bf16 path needs D % 256 == 0
+    fb = feat.to(torch.bfloat16).contiguous()
+    a, _ = gp.lift_mean_fused(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, model.last_keep, fb)
+    b, _ = gp.lift_mean_fused(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, model.last_keep,
+                              fb.float().contiguous())
+    assert torch.equal(a, b)
+
+
+def test_scene_voxel_scatter_mean_bit_exact(scene_run):
+    model, ref = scene_run["model"], scene_run["ref"]
+    order = model.last["index"].order.long().cpu()
+    vin = model.last["voxel_in"].cpu()[:, :134]
+    assert torch.equal(vin, ref["voxel_in"][order])
+
+
+def test_scene_kernel_map(scene_run):
+    from oracle import oracle
+    sc, model = scene_run["sc"], scene_run["model"]
+    idx = model.last["index"]
+    order, rank = idx.order.long().cpu().numpy(), idx.rank.long().cpu().numpy()
+    assert (rank[order] == np.arange(len(order))).all()
+    ref = oracle.kernel_map_fast(sc.voxel_coords)               # original numbering
+    got = model.last["nbr27"].cpu().numpy()                    # sorted numbering
+    exp = ref[order]
+    exp = np.where(exp >= 0, rank[np.maximum(exp, 0)], -1)
+    assert (got == exp).all()
+
+
+def test_scene_knn_bit_exact(scene_run):
+    model, ref = scene_run["model"], scene_run["ref"]
+    knn = model.last["knn_orig"].cpu().numpy().astype(np.int64)
+    assert (knn == ref["knn"]).all(), f"{(knn != ref['knn']).any(1).sum()} rows differ"
+    idx = model.last["index"]
+    order, rank = idx.order.long().cpu().numpy(), idx.rank.long().cpu().numpy()
+    assert (model.last["knn_sorted"].cpu().numpy() == rank[ref["knn"][order]]).all()
+
+
+def test_scene_student_embeddings(scene_run):
+    model, ref = scene_run["model"], scene_run["ref"]
+    order = model.last["index"].order.long().cpu()
+    err = (model.last["embed"].cpu() - ref["embed"][order]).abs().max().item()
+    assert err < 2e-4, f"student embedding max-abs {err}"
+
+
+def test_scene_softmax_weights(scene_run):
+    model, ref = scene_run["model"], scene_run["ref"]
+    order = model.last["index"].order.long().cpu()
+    w = model.last["weights"].cpu()
+    assert w.shape[1] == 16
+    err = (w - ref["weights"][order]).abs().max().item()
+    assert err < 2e-3, f"softmax weight max-abs {err}"     # 20 x amplification of the 2e-4 embedding tolerance
+    assert torch.allclose(w.sum(1), torch.ones(w.shape[0]), atol=1e-5)
+
+
+def test_scene_pooled_features_within_1e3(scene_run):
+    model, ref = scene_run["model"], scene_run["ref"]
+    order = model.last["index"].order.long().cpu()
+    err = (model.last["pooled"].cpu() - ref["pooled_voxels"][order][:, :128]).abs().max().item()
+    assert err < 1e-3, f"pooled max-abs {err} (north star bound 1e-3)"
+
+
+def test_scene_labels_histograms_miou(scene_run):
+    from oracle import oracle
+    sc, out, ref = scene_run["sc"], scene_run["out"], scene_run["ref"]
+    pred = out["pred"].cpu()
+    ref_pred = ref["pred"].clone()
+    lab = torch.as_tensor(sc.labels)
+    ref_pred[lab == sc.ignore_label] = sc.ignore_label
+    # rows whose fp64 top-2 logit margin is tiny may legitimately flip with fp32 summation order
+    lg = ref["logits"].double()
+    top2 = lg.topk(2, dim=1).values
+    safe = (top2[:, 0] - top2[:, 1]) > 1e-4 * sc.logit_scale
+    assert torch.equal(pred[safe], ref_pred[safe])
+    assert int((pred != ref_pred).sum()) == 0, "labels differ on near-tie rows"
+    h = out["hist"].cpu().numpy()
+    assert (h[0] == ref["inter"].numpy()).all() and (h[1] == ref["union"].numpy()).all()
+    assert (h[2] == ref["target"].numpy()).all()
+    from geopurify_b200.validation import mean_iou
+    assert mean_iou(h[0], h[1], h[2]) == oracle.miou(ref["inter"].numpy(), ref["union"].numpy(), ref["target"].numpy())
