@@ -1,0 +1,390 @@
+#!/usr/bin/env python
+"""bench.py -- points/s purified + classified per B200 on ScanNetV2-val-shaped synthetic scenes.
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (one process per GPU under torchrun for N>1)
+    python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the oracle port on the host cores
+
+A "step" is one scene through the whole hot path: project + occlusion test + gather-mean
+lifting over V views, hole fill, voxel scatter-mean, student forward, kNN, affinity softmax, T pooling applications,
+text-embedding classification, IoU histograms.  Scenes are independent, so ranks shard scenes (weak scaling) and the
+only collective is one all-reduce of the [3,C] histogram block after the timed region.
+
+`value`   : points/s with every input already resident in HBM (CUDA events, max over ranks).
+`e2e`     : points/s through `run_scene_host` on pinned HOST buffers: host->device copies of every input, the
+            on-device expansion of the compact 2-D features, the path, and the device->host read of per-point
+            predictions + histograms, all inside the timed region.
+`roofline`: the dominant stage of the step (by device time), achieved algorithmic bytes/s or FLOP/s against the
+            measured peak in MEASURED_PEAKS.json; `stages` carries the same for every stage.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+REF_K, REF_T, REF_SHARPEN = 96, 19, 20.0     # reference models/affinity_module.py:1492-1493, 1584-1587
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=12)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pool", type=int, default=4, help="distinct synthetic scenes per rank, cycled over the steps")
+    ap.add_argument("--points", type=int, default=0, help="fixed N per scene (0: draw from the ScanNet val sizes)")
+    ap.add_argument("--views", type=int, default=50)
+    ap.add_argument("--classes", type=int, default=20)
+    ap.add_argument("--K", type=int, default=REF_K)
+    ap.add_argument("--T", type=int, default=REF_T)
+    ap.add_argument("--feat-dtype", default="bf16", choices=["bf16", "f32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample-points", type=int, default=20000)
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=float(d["hbm_gbs"]), tf_burst=float(d["bf16_tflops"]),
+                    tf_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), source="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
+
+
+def scene_sizes(args, rank):
+    from geopurify_b200 import synth
+    rng = np.random.default_rng(5557 + 1000 * rank)
+    if args.points:
+        return [args.points] * args.pool
+    # first scene of every rank is the headline ~150k-point shape; the rest follow the val size distribution
+    return [150_000] + [synth.scannet_val_size(rng) for _ in range(args.pool - 1)]
+
+
+def make_scenes(args, rank):
+    from geopurify_b200 import synth
+    out = []
+    for i, n in enumerate(scene_sizes(args, rank)):
+        out.append(synth.make_scene(n_points=n, n_views=args.views, image_dim=(320, 240), feat_dim=512,
+                                    n_classes=args.classes, seed=5557 + 1000 * rank + i))
+    return out
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc = index, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            text, _ = self.proc.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+            text, _ = self.proc.communicate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in text.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nme, val in zip(names, f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------- CPU arm (oracle port)
+def cpu_sample_scene(args):
+    """Bounded sample of the workload for the CPU legs: same V-independent shapes (240x320 views, D=512, K, T, C,
+    full-size student), fewer points and views, room shrunk to keep the ScanNet point density."""
+    from geopurify_b200 import synth
+    n = args.cpu_sample_points
+    s = math.sqrt(n / 150_000.0)
+    views = max(4, min(args.views, int(round(args.views * n / 150_000.0)) + 3))
+    sc = synth.make_scene(n_points=n, n_views=views, image_dim=(320, 240), feat_dim=512, n_classes=args.classes,
+                          seed=5557, room=(5.0 * s, 4.0 * s, 2.7), n_boxes=2)
+    desc = (f"1 scene, N={n} points, V={views} views 240x320, D=512, K={args.K}, T={args.T}, C={args.classes}, "
+            f"full student 518-512x9-128, M={sc.voxel_coords.shape[0]} voxels")
+    return sc, desc
+
+
+def cpu_run(args, sc, state, repeats=1):
+    """Times oracle.evaluate_scene (the CPU restatement of the reference path) on the host cores."""
+    import torch
+    from oracle import oracle
+    stages = {}
+    t0 = time.perf_counter()
+    for _ in range(repeats):
+        oracle.evaluate_scene(sc, state, k=args.K, n_iter=args.T, sharpen=REF_SHARPEN, stages=stages)
+    dt = (time.perf_counter() - t0) / repeats
+    return dt, {k: round(v / repeats, 4) for k, v in stages.items()}, torch.get_num_threads()
+
+
+def reference_arm(args):
+    """--impl reference: the reference's own path cannot be installed here (MinkowskiEngine, faiss, torch_scatter,
+    detectron2 are absent and there is no network), so this arm times the oracle port -- numpy /
+    torch-CPU with the same torch calls the reference makes -- on all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    from geopurify_b200 import synth
+    sc, desc = cpu_sample_scene(args)
+    state = synth.make_student_state()
+    for _ in range(min(args.warmup, 1)):
+        cpu_run(args, sc, state)
+    t0 = time.perf_counter()
+    stages = {}
+    for _ in range(args.steps):
+        _, st, threads = cpu_run(args, sc, state)
+        for k, v in st.items():
+            stages[k] = stages.get(k, 0.0) + v
+    dt = time.perf_counter() - t0
+    value = sc.n_points * args.steps / dt
+    line = {
+        "impl": "reference", "metric": "points/sec purified+classified", "value": value, "unit": "points/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args),
+        "cpu_baseline": {"value": value, "unit": "points/s", "cores": threads, "kind": "port", "sample": desc,
+                         "host_cpus": os.cpu_count(),
+                         "stages_s": {k: round(v / args.steps, 4) for k, v in stages.items()}},
+        "e2e": {"value": value, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, sizes=None):
+    cfg = {"workload": "ScanNetV2 val-shaped synthetic scenes (BASELINE.json configs[1]): 50 views 240x320, "
+                       "512-d features, 2 cm voxels, student 518-512x9-128, one scene per step",
+           "views": args.views, "image": "240x320", "feat_dim": 512, "classes": args.classes, "K": args.K,
+           "T": args.T, "sharpen": REF_SHARPEN, "feat_dtype_2d": args.feat_dtype,
+           "scene_pool_per_rank": args.pool, "parallelism": f"scenes sharded over {args.gpus} GPU(s), 1 rank/GPU",
+           "l2": "inputs larger than L2: each step reads a different scene's 3.9 GB feature maps"}
+    if sizes is not None:
+        cfg["points_per_scene"] = sizes
+    return cfg
+
+
+# ----------------------------------------------------------------------------- algorithmic work per stage
+def stage_work(model, s, args, n, m, pairs, distinct_cells, views_kept):
+    """Algorithmic bytes / FLOPs of one scene per stage (DESIGN.md states the same formulas)."""
+    V, D, E, K, T, C = s.w2c.shape[0], 512, 128, args.K, args.T, args.classes
+    fs = 2 if args.feat_dtype == "bf16" else 4
+    h = 512
+    w = {}
+    w["project"] = ("hbm", n * 24 + V * n * 8 + V * n * 4 + V * 160)
+    w["lift"] = ("hbm", n * 24 + distinct_cells * D * fs + n * D * 4 + n)
+    w["fill"] = ("hbm", n * 12 + n + n * 4)
+    w["voxel_mean"] = ("hbm", n * (D + 6) * 4 + n * 4 + m * (D + 6) * 4)
+    w["student"] = ("tensor", 2.0 * (pairs * 544 * h + 8 * pairs * h * h + m * h * E))
+    w["knn"] = ("hbm", m * 16 + m * K * 4)
+    w["affinity"] = ("hbm", m * E * 4 + m * K * 4 + m * K * 4)
+    w["pool"] = ("hbm", T * (2 * m * D * 4 + m * K * 4 + m * E * 4))
+    w["classify"] = ("hbm", m * D * 4 + C * D * 4 + m * 4 + n * (4 + 8) + 3 * C * 8)
+    return w
+
+
+def ours_arm(args):
+    import torch
+    import torch.distributed as dist
+    from geopurify_b200 import _lib, ops, synth
+    from geopurify_b200.affinity_module import (SonataXAffinityTrainer, host_scene_from_synth, run_scene_host,
+                                                upload_scene)
+    from geopurify_b200.student import AffinityPredictor, load_numpy_state
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    _lib.require_cuda()
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pk = peaks()
+    fdt = torch.bfloat16 if args.feat_dtype == "bf16" else torch.float32
+
+    scenes = make_scenes(args, rank)
+    hosts = [host_scene_from_synth(sc) for sc in scenes]
+    state = synth.make_student_state()
+    student = load_numpy_state(AffinityPredictor(518, 128, 512), state)
+    text = scenes[0].text     # same class prompts for every scene (seeded per scene otherwise)
+    model = SonataXAffinityTrainer(text_features=text, logit_scale=100.0, student=student, feature_dim=512, K=args.K,
+                                   n_pool=args.T, sharpen=REF_SHARPEN)
+    ign = torch.tensor([255], dtype=torch.int64, device="cuda")
+    resident = [upload_scene(h, fdt) for h in hosts]
+    torch.cuda.synchronize()
+    npts = [h.n_points for h in hosts]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        pts = 0
+        for i in range(steps):
+            fn(i % len(hosts))
+            pts += npts[i % len(hosts)]
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        tot = torch.tensor([float(pts)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        return float(ms.item()), float(tot.item())
+
+    hist = torch.zeros((3, args.classes), dtype=torch.int64, device="cuda")
+
+    def step_resident(i):
+        model.run_scene(resident[i], hist=hist, ignore=ign)
+
+    feat_buf = torch.empty_like(resident[0].feat)
+
+    def step_host(i):
+        run_scene_host(model, hosts[i], ign, fdt, feat_out=feat_buf if hosts[i].n_points >= 0 else None)
+
+    # ---- device-resident throughput
+    for i in range(args.warmup):
+        step_resident(i % len(hosts))
+    hist.zero_()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = _lib.launch_count
+    ms, pts = timed(step_resident, args.steps)
+    launches = _lib.launch_count - l0
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        dist.all_reduce(hist)          # the path's one exchange step: [3,C] int64 over NCCL
+    from geopurify_b200.validation import mean_iou
+    hsum = hist.cpu().numpy()
+    miou = mean_iou(hsum[0], hsum[1], hsum[2])
+
+    # ---- end to end on host buffers
+    for i in range(min(args.warmup, 3)):
+        step_host(i % len(hosts))
+    ms_e2e, pts_e2e = timed(step_host, args.steps)
+    h2d = float(np.mean([hosts[i % len(hosts)].nbytes for i in range(args.steps)]))
+    d2h = float(np.mean([npts[i % len(hosts)] * 8 + 3 * args.classes * 8 for i in range(args.steps)]))
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- per-stage device times (separate pass, CUDA events at stage boundaries on the launching stream)
+    acc, counts = {}, {}
+    reps = max(2, min(args.steps, 2 * len(hosts)))
+    for r in range(reps):
+        marks = []
+        model.stage_hook = lambda name: marks.append((name, _rec(torch)))
+        model.run_scene(resident[r % len(hosts)], ignore=ign)
+        torch.cuda.synchronize()
+        for (a, ea), (b, eb) in zip(marks[:-1], marks[1:]):
+            acc[b] = acc.get(b, 0.0) + ea.elapsed_time(eb)
+    model.stage_hook = None
+    stage_ms = {k: v / reps for k, v in acc.items()}
+
+    # work of the scenes used in that pass, averaged
+    works = {}
+    for r in range(reps):
+        s = resident[r % len(hosts)]
+        sc = scenes[r % len(hosts)]
+        model.run_scene(s, ignore=ign, keep_intermediates=True)
+        W_, H_ = s.image_dim
+        pix, cnt = ops.project_views(s.coords, s.w2c, s.intr, s.depth, H_, W_, s.cut, s.vis_thres)
+        keep = model.last_keep.bool()
+        vis = pix[keep]
+        vid = torch.arange(vis.shape[0], device="cuda", dtype=torch.int64)[:, None] * (W_ * H_)
+        cells = int(torch.unique((vis.long() + vid)[vis >= 0]).numel())
+        pairs = int((model.last["nbr27"] >= 0).sum())
+        m = model.last["pooled"].shape[0]
+        wk = stage_work(model, s, args, sc.n_points, m, pairs, cells, int(keep.sum()))
+        for k, (b, v) in wk.items():
+            works.setdefault(k, [b, 0.0])[1] += v / reps
+        model.last = {}
+    stages = {}
+    for k, t in stage_ms.items():
+        bound, work = works[k]
+        if bound == "hbm":
+            ach, peak, unit = work / (t * 1e-3) / 1e9, pk["hbm"], "GB/s"
+        else:
+            ach, peak, unit = work / (t * 1e-3) / 1e12, pk["tf_sustained"], "TFLOP/s"
+        stages[k] = {"ms": round(t, 4), "bound": bound, "achieved": round(ach, 2), "peak": peak, "unit": unit,
+                     "frac": round(ach / peak, 4), "share": round(t / sum(stage_ms.values()), 4)}
+    top = max(stage_ms, key=stage_ms.get)
+    launches_in_top = {"pool": args.T}.get(top, None)
+    roof = dict(stages[top])
+    roof.update({"kernel": top, "traffic": None, "peak_source": pk["source"],
+                 "launches_per_step": launches_in_top,
+                 "avg_launch_ms": round(stage_ms[top] / launches_in_top, 4) if launches_in_top else None})
+
+    line = {
+        "metric": "points/sec purified+classified", "value": pts / (ms * 1e-3), "unit": "points/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, npts),
+        "scenes_per_s": world * args.steps / (ms * 1e-3),
+        "e2e": {"value": pts_e2e / (ms_e2e * 1e-3), "unit": "points/s", "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "api": "geopurify_b200.affinity_module.run_scene_host"},
+        "gpu_launches": launches, "clocks": clocks, "roofline": roof, "stages": stages,
+        "miou_synthetic": miou[0],
+    }
+    if not args.no_cpu_baseline and world == 1:
+        sc, desc = cpu_sample_scene(args)
+        dt, st, threads = cpu_run(args, sc, state)
+        line["cpu_baseline"] = {"value": sc.n_points / dt, "unit": "points/s", "cores": threads, "kind": "port",
+                                "sample": desc, "host_cpus": os.cpu_count(), "seconds": round(dt, 2), "stages_s": st}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def _rec(torch):
+    e = torch.cuda.Event(enable_timing=True)
+    e.record()
+    return e
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        reference_arm(a)
+    else:
+        ours_arm(a)

@@ -73,6 +73,11 @@ class SonataXAffinityTrainer:
         self.min_visible = min_visible
         self.fill_cell = fill_cell
         self.last = {}
+        self.stage_hook = None   # optional callable(name) invoked at stage boundaries (bench.py records CUDA events)
+
+    def _mark(self, name):
+        if self.stage_hook is not None:
+            self.stage_hook(name)
 
     def eval(self):
         return self
@@ -123,11 +128,16 @@ class SonataXAffinityTrainer:
         vin = torch.zeros((m, stride), dtype=torch.float32, device=lifted.device)
         plan.mean(lifted, d, vin, 0)
         plan.mean(gauss, 6, vin, d)
+        self._mark("voxel_mean")
         nbr27 = index.kernel_map()
         embed = self.affinity_student.forward_sorted(vin, nbr27, normalize=True)
+        self._mark("student")
         nbr_orig, nbr_sorted = index.knn(self.K, want_orig=keep_intermediates, want_sorted=True)
+        self._mark("knn")
         w = ops.affinity_softmax(embed, nbr_sorted, self.affinity_sharpen_factor)
+        self._mark("affinity")
         pooled = ops.pool(vin, d, nbr_sorted, w, self.n_pool)
+        self._mark("pool")
         if keep_intermediates:
             self.last = dict(index=index, voxel_in=vin, embed=embed, knn_orig=nbr_orig, knn_sorted=nbr_sorted,
                              weights=w, pooled=pooled, p2v_sorted=p2v_sorted, nbr27=nbr27)
@@ -150,16 +160,20 @@ class SonataXAffinityTrainer:
 
     # ------------------------------------------------------------------ B200-first whole-scene path
     @torch.no_grad()
-    def run_scene(self, s: SceneInputs, hist=None, ignore=None, keep_intermediates=False):
+    def run_scene(self, s: SceneInputs, hist=None, ignore=None, keep_intermediates=False, want_pred=False):
         """Stages 1a-4 on the device: fused project + gather-mean, fill, purify, per-voxel classification,
         label gather + IoU histograms.  Returns dict(labels_voxel, p2v_sorted, hist, seen)."""
         W, H = s.image_dim
         d = self.feature_dim
+        self._mark("begin")
         _, counts = ops.project_views(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres)
         keep = ops.accept_views(counts, self.min_visible)
+        self._mark("project")
         lifted, seen = ops.lift_mean_fused(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, keep, s.feat)
+        self._mark("lift")
         nn = ops.nn1_fill(s.coords_f32, seen, self.fill_cell)
         ops.copy_rows(lifted, d, nn)
+        self._mark("fill")
         if keep_intermediates:
             self.last_lifted, self.last_seen, self.last_keep, self.last_counts = lifted, seen, keep, counts
         pooled, p2v_sorted = self.purify(lifted, s.gauss, s.voxel_coords, s.p2v, s.extent, keep_intermediates)
@@ -168,7 +182,8 @@ class SonataXAffinityTrainer:
         if s.labels is not None:
             c = self.text_features.shape[0]
             out["hist"], out["pred"] = ops.iou_hist(labels_vox, p2v_sorted, s.labels, ignore, c, hist,
-                                                    want_pred=keep_intermediates)
+                                                    want_pred=keep_intermediates or want_pred)
+        self._mark("classify")
         return out
 
 
@@ -197,3 +212,67 @@ def scene_inputs_from_synth(scene, feat_dtype=torch.bfloat16, device="cuda", coo
                        intr=intr_d, depth=torch.as_tensor(scene.depth).to(dev).contiguous(), feat=feat,
                        image_dim=(W, H), cut=scene.cut, vis_thres=scene.vis_thres,
                        labels=torch.as_tensor(scene.labels).to(dev))
+
+
+# ---------------------------------------------------------------------- host-buffer entry (the e2e call)
+HOST_FIELDS = ("coords", "coords_f32", "gauss", "voxel_coords", "p2v", "w2c", "intr", "depth", "idmaps", "tables",
+               "labels")
+
+
+@dataclass
+class HostScene:
+    """One scene as pinned HOST tensors -- what a caller holds after the data loader and the 2-D VLM
+    (the VLM output in its compact (id map, embedding table) form).  `nbytes` is what one upload moves."""
+    t: dict
+    extent: tuple
+    image_dim: tuple
+    cut: int
+    vis_thres: float
+
+    @property
+    def nbytes(self):
+        return sum(v.numel() * v.element_size() for v in self.t.values())
+
+    @property
+    def n_points(self):
+        return self.t["coords"].shape[0]
+
+
+def host_scene_from_synth(scene, pin=True):
+    from .synth import mapper_intrinsics
+    k = mapper_intrinsics(scene.intrinsics, scene.image_dim)
+    V = scene.n_views
+    intr = np.repeat(np.array([[k[0, 0], k[1, 1], k[0, 2], k[1, 2]]], dtype=np.float64), V, 0)
+    t = dict(coords=torch.as_tensor(scene.coords.astype(np.float64)),
+             coords_f32=torch.as_tensor(scene.coords),
+             gauss=torch.as_tensor(scene.gauss),
+             voxel_coords=torch.as_tensor(scene.voxel_coords.astype(np.int32)),
+             p2v=torch.as_tensor(scene.inds_reconstruct.astype(np.int32)),
+             w2c=torch.as_tensor(scene.w2c.astype(np.float64).reshape(V, 16)),
+             intr=torch.as_tensor(intr),
+             depth=torch.as_tensor(scene.depth),
+             idmaps=torch.as_tensor(scene.idmaps),
+             tables=torch.as_tensor(scene.tables),
+             labels=torch.as_tensor(scene.labels))
+    t = {n: (v.contiguous().pin_memory() if pin else v.contiguous()) for n, v in t.items()}
+    extent = tuple(int(e) + 1 for e in scene.voxel_coords.max(0))
+    return HostScene(t=t, extent=extent, image_dim=tuple(scene.image_dim), cut=scene.cut, vis_thres=scene.vis_thres)
+
+
+def upload_scene(h: HostScene, feat_dtype=torch.bfloat16, feat_out=None):
+    """Host -> device copies of every field (async on the current stream, pinned sources) + the dense feature map
+    built on the device from (idmaps, tables).  Returns SceneInputs."""
+    d = {n: v.cuda(non_blocking=True) for n, v in h.t.items()}
+    feat = ops.expand_idmap(d["idmaps"], d["tables"], feat_dtype, out=feat_out)
+    return SceneInputs(coords=d["coords"], coords_f32=d["coords_f32"], gauss=d["gauss"],
+                       voxel_coords=d["voxel_coords"], p2v=d["p2v"], extent=h.extent, w2c=d["w2c"], intr=d["intr"],
+                       depth=d["depth"], feat=feat, image_dim=h.image_dim, cut=h.cut, vis_thres=h.vis_thres,
+                       labels=d["labels"])
+
+
+def run_scene_host(model, h: HostScene, ignore, feat_dtype=torch.bfloat16, feat_out=None):
+    """End-to-end call on HOST buffers: upload, purify + classify, read back per-point predictions and the
+    IoU histogram block.  Returns (pred [N] int64 CPU, hist [3,C] int64 CPU)."""
+    s = upload_scene(h, feat_dtype, feat_out)
+    out = model.run_scene(s, ignore=ignore, want_pred=True)
+    return out["pred"].cpu(), out["hist"].cpu()

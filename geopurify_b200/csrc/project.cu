@@ -430,3 +430,56 @@ extern "C" int gp_lift_mean_pix(const int32_t* pix, int64_t n, int V, int H, int
   return launch_lift<float, 0, true>(nullptr, n, nullptr, nullptr, nullptr, V, H, W, 0, 0.0, keep, pix, feat,
                                      feat_dtype, D, out, out_stride, seen, (cudaStream_t)stream);
 }
+
+// ------------------------------------------------------------------ gp_expand_idmap
+// Dense channels-last map from the (id map, embedding table) form: feat[v,h,w,:] = table[v, id[v,h,w], :].
+// Stand-in for the 2-D VLM's per-pixel output (out of scope); also the A5 "mask embedding" lookup
+// (reference models/affinity_module.py:584-592) materialised per pixel.
+template <bool BF16>
+__global__ void __launch_bounds__(256) expand_idmap_kernel(const uint8_t* __restrict__ idmap,
+                                                            const float* __restrict__ table, int64_t pixels_per_view,
+                                                            int64_t total_pixels, int Q, int D,
+                                                            void* __restrict__ feat) {
+  const int chunks = D >> 3;  // 8 channels per thread
+  const int64_t total = total_pixels * chunks;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    int64_t p = t / chunks;
+    int c = (int)(t - p * chunks) << 3;
+    int v = (int)(p / pixels_per_view);
+    int q = idmap[p];
+    const float4* src = (const float4*)(table + ((int64_t)v * Q + q) * D + c);
+    float4 a = __ldg(src), b = __ldg(src + 1);
+    if (BF16) {
+      __nv_bfloat162 h0 = __floats2bfloat162_rn(a.x, a.y), h1 = __floats2bfloat162_rn(a.z, a.w);
+      __nv_bfloat162 h2 = __floats2bfloat162_rn(b.x, b.y), h3 = __floats2bfloat162_rn(b.z, b.w);
+      uint4 o;
+      o.x = *(unsigned*)&h0;
+      o.y = *(unsigned*)&h1;
+      o.z = *(unsigned*)&h2;
+      o.w = *(unsigned*)&h3;
+      *(uint4*)((__nv_bfloat16*)feat + p * D + c) = o;
+    } else {
+      float4* dst = (float4*)((float*)feat + p * D + c);
+      dst[0] = a;
+      dst[1] = b;
+    }
+  }
+}
+
+extern "C" int gp_expand_idmap(const uint8_t* idmap, const float* table, int V, int H, int W, int Q, int D,
+                               void* feat, int feat_dtype, gp_stream_t stream) {
+  GP_CHECK_ARG(V >= 0 && H > 0 && W > 0 && Q > 0 && Q <= 256 && D > 0 && D % 8 == 0, "gp_expand_idmap: bad sizes");
+  GP_CHECK_ARG(feat_dtype == GP_F32 || feat_dtype == GP_BF16, "gp_expand_idmap: feature dtype");
+  GP_CHECK_ARG(((uintptr_t)table % 16) == 0 && ((uintptr_t)feat % 16) == 0, "gp_expand_idmap: alignment");
+  int64_t ppv = (int64_t)H * W, total = ppv * V;
+  if (total == 0) return GP_OK;
+  int64_t blocks = (total * (D / 8) + 255) / 256;
+  int64_t cap = (int64_t)GP_SM_COUNT * 8 * 8;
+  unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
+  if (feat_dtype == GP_BF16)
+    expand_idmap_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(idmap, table, ppv, total, Q, D, feat);
+  else
+    expand_idmap_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(idmap, table, ppv, total, Q, D, feat);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}

@@ -85,6 +85,19 @@ def lift_mean_fused(coords, w2c, intr, depth, H, W, cut, vis_thres, keep, feat, 
     return out, seen
 
 
+def expand_idmap(idmap_u8, table_f32, dtype=torch.bfloat16, out=None):
+    """feat[v,h,w,:] = table[v, idmap[v,h,w], :] as a dense channels-last map (the 2-D VLM stand-in)."""
+    lib = L.load()
+    V, H, W = idmap_u8.shape
+    Q, D = table_f32.shape[1], table_f32.shape[2]
+    if out is None:
+        out = torch.empty((V, H, W, D), dtype=dtype, device=_dev())
+    L.check(lib.gp_expand_idmap(L.ptr(idmap_u8), L.ptr(table_f32), V, H, W, Q, D, L.ptr(out), L.dtype_code(out),
+                                L.stream()))
+    L.count(1)
+    return out
+
+
 def lift_mean_pix(pix, keep, feat, H, W, out=None, out_stride=None):
     lib = L.load()
     V, n = pix.shape

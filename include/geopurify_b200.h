@@ -75,6 +75,12 @@ int gp_lift_mean_fused(const void* coords, int coords_dtype, int64_t n, const do
                        const uint8_t* keep, const void* feat, int feat_dtype, int D, float* out,
                        int64_t out_stride, uint8_t* seen, gp_stream_t stream);
 
+/* ---- 2-D feature form conversion: feat[v,h,w,:] = table[v, idmap[v,h,w], :] (the per-pixel view of the mask
+ * embedding lookup at models/affinity_module.py:584-592; also the synthetic stand-in for the 2-D VLM output).
+ *   idmap [V,H,W] uint8, table [V,Q,D] float32, feat (out) [V,H,W,D] float32 or bf16, D % 8 == 0 */
+int gp_expand_idmap(const uint8_t* idmap, const float* table, int V, int H, int W, int Q, int D, void* feat,
+                    int feat_dtype, gp_stream_t stream);
+
 /* ---- A4 from precomputed pixels (the reference's x_label / y_label / mask_2d form): same gather-mean, pix from
  * gp_project_views or from the reference data loader. */
 int gp_lift_mean_pix(const int32_t* pix, int64_t n, int V, int H, int W, const uint8_t* keep, const void* feat,
