@@ -1,0 +1,683 @@
+// Student affinity network on the 5th-gen tensor cores (tcgen05 + TMEM), fp32-faithful through a bf16x3 split.
+// Replaces AffinityPredictor.forward on MinkowskiEngine (reference models/affinity_module.py:33-72, 1541-1547).
+//
+// A sparse 3^3 convolution is  out[i] = sum_o W_o^T in[nbr(i,o)]  over the occupied offsets only (~4.9 of 27 per
+// voxel on ScanNet-density surfaces), so the work is organised by (output, input) PAIRS, not by output tiles:
+//   1. pair lists: for every slab of SLAB output voxels and every offset o, the pairs (i, nbr(i,o)) in voxel order
+//      (flags -> exclusive scan -> fill); 128-pair tiles never straddle an offset.
+//   2. gather-GEMM (this file's main kernel): C[p, :] = in[pair_in[p], :] W_o for every pair p, one 128 x N tile per
+//      CTA iteration.  A rows are gathered with cp.async (zero-filled tails) from activations stored as bf16 hi/lo
+//      planes, W_o^T tiles arrive by TMA, both in the 32-byte-swizzled K-major layout UMMA reads.  Each K=16 step
+//      issues  Ahi*Bhi + Ahi*Blo + Alo*Bhi  into a 128 x N fp32 accumulator in TMEM; the epilogue warps drain TMEM
+//      to a pair-major staging buffer with coalesced 128-byte row stores.
+//   3. reduce (student_reduce_kernel): out[i] = sum of its staged pair rows in ascending offset order (the oracle's
+//      order, deterministic, no atomics), BN scale/shift, residual, ReLU, then the bf16 hi/lo split for the next layer.
+#include <cub/device/device_scan.cuh>
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace {
+
+constexpr int TM = 128;        // pairs (rows) per tile = UMMA M
+constexpr int BK = 16;         // K per stage = UMMA K for bf16; 32-byte operand rows, SWIZZLE_32B
+constexpr int ROWB = BK * 2;   // bytes per operand row per stage
+constexpr int NSTAGE = 5;
+constexpr int LAG = 3;         // cp.async groups in flight per producer thread
+constexpr int EPI_LD = 36;     // floats per staged row in the epilogue transpose buffer (16-byte aligned, conflict-free)
+constexpr int NTHREADS = 384;  // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue, 8-11 A gather
+
+struct TileInfo {  // one 128-pair tile
+  int offset;      // kernel offset o (selects W_o)
+  int p0;          // first pair (index into pair_in); identity mode: first input row
+  int nrows;       // valid rows (<= 128)
+  int c_row0;      // first row of the tile in C
+};
+
+template <int N>
+struct Smem {
+  static constexpr int A_BYTES = TM * ROWB;         // per plane
+  static constexpr int B_BYTES = N * ROWB;          // per plane
+  static constexpr int STAGE = 2 * A_BYTES + 2 * B_BYTES;
+  static constexpr int EPI = 4 * 32 * EPI_LD * 4;
+  static constexpr int BAR_OFF = NSTAGE * STAGE + EPI;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024;  // barriers + slack for the 1024-byte alignment of the base
+};
+
+struct GemmParams {
+  const __nv_bfloat16* a;  // activations [rows][2][kp]: hi plane then lo plane
+  int64_t lda;             // elements between rows (= 2 * kp)
+  int kp;                  // padded K (multiple of 16)
+  const int32_t* pair_in;  // gathered input row per pair, or nullptr (identity)
+  const TileInfo* tiles;   // tile table, or nullptr (identity: tile t covers rows [128 t, 128 t + 128))
+  const int32_t* ntiles_dev;  // number of tiles (device), or nullptr -> ntiles_host
+  int ntiles_host;
+  int64_t m_rows;          // identity mode: number of rows
+  int cout_total;          // rows per (offset, plane) block of the packed weights (= layer cout)
+  float* c;                // [c_rows][ldc]
+  int64_t ldc;
+};
+
+template <int N>
+__global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __grid_constant__ CUtensorMap wmap,
+                                                                      const GemmParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  using S = Smem<N>;
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  float* epi = (float*)(smem + NSTAGE * S::STAGE);
+  uint64_t* bars = (uint64_t*)(smem + S::BAR_OFF);
+  uint64_t* full = bars;                   // [NSTAGE] A gathered + B landed
+  uint64_t* empty = bars + NSTAGE;         // [NSTAGE] MMAs reading the stage have completed
+  uint64_t* tmem_full = bars + 2 * NSTAGE;  // accumulator complete
+  uint64_t* tmem_empty = tmem_full + 1;     // accumulator drained
+  uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ntiles = P.ntiles_dev ? *P.ntiles_dev : P.ntiles_host;
+  const int ksteps = P.kp / BK;
+
+  if (threadIdx.x == 0) {
+    tc::tma_prefetch_desc(&wmap);
+    for (int s = 0; s < NSTAGE; ++s) {
+      tc::mbar_init(&full[s], 4 + 1);  // 4 gather warps + the TMA thread's expect_tx arrive
+      tc::mbar_init(&empty[s], 1);
+    }
+    tc::mbar_init(tmem_full, 1);
+    tc::mbar_init(tmem_empty, 4);
+    tc::fence_barrier_init();
+  }
+  if (warp == 2) tc::tmem_alloc<N>(tmem_slot);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  auto tile_of = [&](int t) -> TileInfo {
+    if (P.tiles) return P.tiles[t];
+    TileInfo ti;
+    ti.offset = 0;
+    ti.p0 = t * TM;
+    int64_t left = P.m_rows - (int64_t)t * TM;
+    ti.nrows = left < TM ? (int)left : TM;
+    ti.c_row0 = t * TM;
+    return ti;
+  };
+
+  if (warp == 0) {
+    // ===================== TMA producer: W_o^T[k0:k0+16] hi + lo for all N outputs =====================
+    if (lane == 0) {
+      uint32_t it = 0;
+      constexpr int BOX = N < 256 ? N : 256;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const TileInfo ti = tile_of(t);
+        for (int ks = 0; ks < ksteps; ++ks, ++it) {
+          const int s = it % NSTAGE;
+          const uint32_t ph = (it / NSTAGE) & 1;
+          tc::mbar_wait(&empty[s], ph ^ 1);
+          tc::mbar_arrive_expect_tx(&full[s], 2 * S::B_BYTES);
+          uint8_t* st = smem + s * S::STAGE + 2 * S::A_BYTES;
+#pragma unroll
+          for (int plane = 0; plane < 2; ++plane)
+#pragma unroll
+            for (int nb = 0; nb < N / BOX; ++nb)
+              tc::tma_load_2d(tc::smem_u32(st + plane * S::B_BYTES + nb * BOX * ROWB), &wmap, ks * BK,
+                              (ti.offset * 2 + plane) * P.cout_total + nb * BOX, &full[s]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint64_t DBASE = tc::umma_desc_kmajor_base<ROWB>();
+    constexpr int UN = N < 256 ? N : 256;
+    constexpr uint32_t IDESC = tc::umma_idesc_bf16(TM, UN);
+    uint32_t it = 0, tcount = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
+      tc::mbar_wait(tmem_empty, (tcount & 1) ^ 1);
+      tc::tc_fence_after();
+      for (int ks = 0; ks < ksteps; ++ks, ++it) {
+        const int s = it % NSTAGE;
+        const uint32_t ph = (it / NSTAGE) & 1;
+        tc::mbar_wait(&full[s], ph);
+        tc::tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_hi = tc::smem_u32(smem + s * S::STAGE);
+          const uint32_t a_lo = a_hi + S::A_BYTES;
+          const uint32_t b_hi = a_hi + 2 * S::A_BYTES;
+          const uint32_t b_lo = b_hi + S::B_BYTES;
+#pragma unroll
+          for (int h = 0; h < N / UN; ++h) {
+            const uint32_t d = tmem_base + h * UN;
+            const uint32_t boff = h * UN * ROWB;
+            // small terms first, then the leading product
+            tc::umma_bf16(d, tc::umma_desc(DBASE, a_lo), tc::umma_desc(DBASE, b_hi + boff), IDESC, ks > 0);
+            tc::umma_bf16(d, tc::umma_desc(DBASE, a_hi), tc::umma_desc(DBASE, b_lo + boff), IDESC, 1);
+            tc::umma_bf16(d, tc::umma_desc(DBASE, a_hi), tc::umma_desc(DBASE, b_hi + boff), IDESC, 1);
+          }
+          tc::umma_commit(&empty[s]);
+          if (ks == ksteps - 1) tc::umma_commit(tmem_full);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ===================== epilogue: TMEM -> registers -> smem transpose -> coalesced global rows =====================
+    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    float* buf = epi + q * 32 * EPI_LD;
+    uint32_t tcount = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
+      const TileInfo ti = tile_of(t);
+      tc::mbar_wait(tmem_full, tcount & 1);
+      tc::tc_fence_after();
+      const int rows_here = ti.nrows - q * 32;  // valid rows in this warp's quadrant
+      float* crow = P.c + ((int64_t)ti.c_row0 + q * 32) * P.ldc;
+      for (int ch = 0; ch < N / 32; ++ch) {
+        uint32_t v[32];
+        tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ch * 32, v);
+        tc::tmem_ld_wait();
+        if (ch == N / 32 - 1) {  // accumulator fully read: the next tile's MMAs may start
+          tc::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(tmem_empty);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *(float4*)(buf + lane * EPI_LD + j * 4) =
+              make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                          __uint_as_float(v[4 * j + 3]));
+        __syncwarp();
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr) {
+          const int row = rr * 4 + (lane >> 3), c4 = lane & 7;
+          if (row < rows_here) {
+            float4 o = *(const float4*)(buf + row * EPI_LD + c4 * 4);
+            *(float4*)(crow + (int64_t)row * P.ldc + ch * 32 + c4 * 4) = o;
+          }
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp >= 8) {
+    // ===================== A gather: thread r owns tile row r =====================
+    const int r = threadIdx.x - 256;
+    const uint32_t swz = (r >> 2) & 1;  // SWIZZLE_32B: 16-byte chunk c of row r is stored at chunk c ^ ((r >> 2) & 1)
+    uint32_t it = 0, signalled = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      const TileInfo ti = tile_of(t);
+      int in_row = -1;
+      if (r < ti.nrows) in_row = P.pair_in ? __ldg(P.pair_in + ti.p0 + r) : ti.p0 + r;
+      const __nv_bfloat16* src = P.a + (int64_t)(in_row < 0 ? 0 : in_row) * P.lda;
+      const uint32_t nbytes = in_row < 0 ? 0u : 16u;
+      for (int ks = 0; ks < ksteps; ++ks, ++it) {
+        const int s = it % NSTAGE;
+        const uint32_t ph = (it / NSTAGE) & 1;
+        tc::mbar_wait(&empty[s], ph ^ 1);
+        const uint32_t dst = tc::smem_u32(smem + s * S::STAGE) + r * ROWB;
+        const __nv_bfloat16* g = src + ks * BK;
+        tc::cp_async16(dst + ((0 ^ swz) << 4), g, nbytes);
+        tc::cp_async16(dst + ((1 ^ swz) << 4), g + 8, nbytes);
+        tc::cp_async16(dst + S::A_BYTES + ((0 ^ swz) << 4), g + P.kp, nbytes);
+        tc::cp_async16(dst + S::A_BYTES + ((1 ^ swz) << 4), g + P.kp + 8, nbytes);
+        tc::cp_async_commit();
+        if (it >= LAG) {  // the group issued LAG iterations ago has landed
+          tc::cp_async_wait<LAG>();
+          tc::fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(&full[signalled % NSTAGE]);
+          ++signalled;
+        }
+      }
+    }
+    tc::cp_async_wait<0>();
+    tc::fence_proxy_async();
+    __syncwarp();
+    for (; signalled < it; ++signalled)
+      if (lane == 0) tc::mbar_arrive(&full[signalled % NSTAGE]);
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc<N>(tmem_base);
+}
+
+
+// ------------------------------------------------------------------ pair lists and tile tables
+// flat index of (slab, offset, row-in-slab): all pairs of one (slab, offset) group are contiguous after the scan
+__device__ __forceinline__ int64_t group_index(int slab, int o, int sl, int S) { return ((int64_t)slab * 27 + o) * S + sl; }
+
+__global__ void tc_pair_flags_kernel(const int32_t* __restrict__ nbr27, int64_t m, int S, int64_t total,
+                                     int32_t* __restrict__ flags) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t > total) return;
+  int f = 0;
+  if (t < total) {
+    int sl = (int)(t % S);
+    int64_t g = t / S;
+    int o = (int)(g % 27);
+    int64_t s = (g / 27) * S + sl;
+    f = (s < m) && (nbr27[s * 27 + o] >= 0);
+  }
+  flags[t] = f;
+}
+
+__global__ void tc_pair_fill_kernel(const int32_t* __restrict__ nbr27, const int32_t* __restrict__ pos, int64_t m,
+                                    int S, int64_t total, int32_t* __restrict__ pair_in) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  int sl = (int)(t % S);
+  int64_t g = t / S;
+  int o = (int)(g % 27);
+  int64_t s = (g / 27) * S + sl;
+  if (s < m) {
+    int nb = nbr27[s * 27 + o];
+    if (nb >= 0) pair_in[pos[t]] = nb;
+  }
+}
+
+// one block per slab: tile table + first tile of every (slab, offset) group
+__global__ void tc_build_tiles_kernel(const int32_t* __restrict__ pos, int S, int max_tiles,
+                                      TileInfo* __restrict__ tiles, int32_t* __restrict__ ntiles,
+                                      int32_t* __restrict__ gtile0) {
+  __shared__ int s_t0[28], s_p0[28];
+  const int slab = blockIdx.x;
+  if (threadIdx.x == 0) {
+    int run = 0;
+    for (int o = 0; o < 27; ++o) {
+      int p0 = pos[group_index(slab, o, 0, S)], p1 = pos[group_index(slab, o, 0, S) + S];
+      s_t0[o] = run;
+      s_p0[o] = p0;
+      gtile0[slab * 27 + o] = run;
+      run += (p1 - p0 + TM - 1) / TM;
+    }
+    s_t0[27] = run;
+    s_p0[27] = pos[group_index(slab, 26, 0, S) + S];
+    ntiles[slab] = run;
+  }
+  __syncthreads();
+  TileInfo* tt = tiles + (int64_t)slab * max_tiles;
+  for (int o = 0; o < 27; ++o) {
+    int nt = s_t0[o + 1] - s_t0[o];
+    int cnt = s_p0[o + 1] - s_p0[o];
+    for (int i = threadIdx.x; i < nt; i += blockDim.x) {
+      TileInfo ti;
+      ti.offset = o;
+      ti.p0 = s_p0[o] + i * TM;
+      ti.nrows = min(TM, cnt - i * TM);
+      ti.c_row0 = (s_t0[o] + i) * TM;
+      tt[s_t0[o] + i] = ti;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ fp32 -> bf16 hi/lo planes
+__device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+  hi = __float2bfloat16_rn(v);
+  lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+}
+
+__global__ void tc_split_input_kernel(const float* __restrict__ x, int64_t stride, int cin, int kp, int64_t m,
+                                      __nv_bfloat16* __restrict__ out) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= m * kp) return;
+  int64_t r = t / kp;
+  int c = (int)(t - r * kp);
+  float v = c < cin ? x[r * stride + c] : 0.f;
+  __nv_bfloat16 hi, lo;
+  split_bf16(v, hi, lo);
+  out[r * 2 * kp + c] = hi;
+  out[r * 2 * kp + kp + c] = lo;
+}
+
+// weights [kv][cin_pad][cout] fp32 -> Wt [kv][2][cout][kp] bf16 (K-major rows, hi plane then lo plane)
+__global__ void tc_pack_weights_kernel(const float* __restrict__ w, int kv, int cin_pad, int cout, int kp,
+                                       __nv_bfloat16* __restrict__ out) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t total = (int64_t)kv * cout * kp;
+  if (t >= total) return;
+  int k = (int)(t % kp);
+  int n = (int)((t / kp) % cout);
+  int o = (int)(t / ((int64_t)kp * cout));
+  float v = k < cin_pad ? w[((int64_t)o * cin_pad + k) * cout + n] : 0.f;
+  __nv_bfloat16 hi, lo;
+  split_bf16(v, hi, lo);
+  out[(((int64_t)o * 2 + 0) * cout + n) * kp + k] = hi;
+  out[(((int64_t)o * 2 + 1) * cout + n) * kp + k] = lo;
+}
+
+// ------------------------------------------------------------------ reduce: pair rows -> output rows + epilogue
+// one warp per output voxel of the slab; COUT = 128 * NV4
+template <int NV4>
+__global__ void __launch_bounds__(256) student_reduce_kernel(const float* __restrict__ staging,
+                                                              const int32_t* __restrict__ nbr27,
+                                                              const int32_t* __restrict__ pos,
+                                                              const int32_t* __restrict__ gtile0, int slab, int S,
+                                                              int64_t m, const float* __restrict__ scale,
+                                                              const float* __restrict__ shift,
+                                                              const float* __restrict__ residual, int relu,
+                                                              __nv_bfloat16* __restrict__ out_hilo,
+                                                              float* __restrict__ out_f32) {
+  constexpr int COUT = 128 * NV4;
+  const int lane = threadIdx.x & 31;
+  const int sl = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t s = (int64_t)slab * S + sl;
+  if (sl >= S || s >= m) return;
+  int row = -1;
+  if (lane < 27 && __ldg(nbr27 + s * 27 + lane) >= 0) {
+    int64_t gi = group_index(slab, lane, 0, S);
+    int rel = __ldg(pos + gi + sl) - __ldg(pos + gi);
+    row = (__ldg(gtile0 + slab * 27 + lane) + rel / TM) * TM + rel % TM;
+  }
+  unsigned live = __ballot_sync(0xffffffffu, row >= 0);
+  float4 acc[NV4];
+#pragma unroll
+  for (int j = 0; j < NV4; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+  while (live) {  // ascending offset order, as the oracle's per-offset index_add_
+    int o = __ffs(live) - 1;
+    live &= live - 1;
+    int rr = __shfl_sync(0xffffffffu, row, o);
+    const float4* src = (const float4*)(staging + (int64_t)rr * COUT);
+    float4 t[NV4];
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) t[j] = ldg_stream_f4(src + j * 32 + lane);
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) {
+      acc[j].x += t[j].x;
+      acc[j].y += t[j].y;
+      acc[j].z += t[j].z;
+      acc[j].w += t[j].w;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NV4; ++j) {
+    const int c = (j * 32 + lane) * 4;
+    float4 v = acc[j];
+    if (scale) {
+      float4 sc = __ldg((const float4*)(scale + c)), sh = __ldg((const float4*)(shift + c));
+      v.x = fmaf(v.x, sc.x, sh.x);
+      v.y = fmaf(v.y, sc.y, sh.y);
+      v.z = fmaf(v.z, sc.z, sh.z);
+      v.w = fmaf(v.w, sc.w, sh.w);
+    }
+    if (residual) {
+      float4 r = __ldg((const float4*)(residual + s * COUT + c));
+      v.x += r.x;
+      v.y += r.y;
+      v.z += r.z;
+      v.w += r.w;
+    }
+    if (relu) {
+      v.x = fmaxf(v.x, 0.f);
+      v.y = fmaxf(v.y, 0.f);
+      v.z = fmaxf(v.z, 0.f);
+      v.w = fmaxf(v.w, 0.f);
+    }
+    if (out_f32) *(float4*)(out_f32 + s * COUT + c) = v;
+    if (out_hilo) {
+      __nv_bfloat16 h[4], l[4];
+      split_bf16(v.x, h[0], l[0]);
+      split_bf16(v.y, h[1], l[1]);
+      split_bf16(v.z, h[2], l[2]);
+      split_bf16(v.w, h[3], l[3]);
+      *(uint2*)(out_hilo + s * 2 * COUT + c) = *(const uint2*)h;
+      *(uint2*)(out_hilo + s * 2 * COUT + COUT + c) = *(const uint2*)l;
+    }
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ host side
+#define GP_TC_SLAB 32768
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// 2-D bf16 tensor [rows][kp] (kp contiguous), box 16 x box_rows, 32-byte swizzle
+static bool make_weight_map(CUtensorMap* map, const void* base, int64_t rows, int kp, int box_rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return false;
+  cuuint64_t dims[2] = {(cuuint64_t)kp, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)kp * 2};
+  cuuint32_t box[2] = {BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+struct TcLayout {
+  int S, nslab, max_tiles, hidden, kp0;
+  int64_t total;  // flag entries
+  size_t off_flags, off_pos, off_pair_in, off_tiles, off_ntiles, off_gtile0, off_xin, off_act[3], off_res[2],
+      off_staging, off_cub, cub_bytes, bytes;
+};
+
+static bool tc_layout(const gp_student_desc* d, int64_t m, TcLayout& L) {
+  if (!d || d->n_layers < 2 || d->n_layers > 16 || m < 0 || m >= (1ll << 31) / 27) return false;
+  int hidden = d->cout[0];
+  for (int l = 0; l + 1 < d->n_layers; ++l)
+    if (d->cout[l] != hidden || d->kv[l] != 27) return false;
+  if (d->kv[d->n_layers - 1] != 1) return false;
+  L.hidden = hidden;
+  L.kp0 = d->cin[0];
+  int64_t m128 = (m + TM - 1) / TM * TM;
+  L.S = (int)(m128 < GP_TC_SLAB ? (m128 > 0 ? m128 : TM) : GP_TC_SLAB);
+  L.nslab = (int)((m + L.S - 1) / L.S);
+  if (L.nslab < 1) L.nslab = 1;
+  L.max_tiles = 27 * (L.S / TM) + 27;
+  L.total = (int64_t)L.nslab * 27 * L.S;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off += gp_align_up(bytes, 1024);
+    return o;
+  };
+  L.off_flags = take(sizeof(int32_t) * (L.total + 1));
+  L.off_pos = take(sizeof(int32_t) * (L.total + 1));
+  L.off_pair_in = take(sizeof(int32_t) * L.total);
+  L.off_tiles = take(sizeof(TileInfo) * (size_t)L.nslab * L.max_tiles);
+  L.off_ntiles = take(sizeof(int32_t) * L.nslab);
+  L.off_gtile0 = take(sizeof(int32_t) * L.nslab * 27);
+  L.off_xin = take(sizeof(__nv_bfloat16) * 2 * (size_t)m * L.kp0);
+  for (int i = 0; i < 3; ++i) L.off_act[i] = take(sizeof(__nv_bfloat16) * 2 * (size_t)m * hidden);
+  for (int i = 0; i < 2; ++i) L.off_res[i] = take(sizeof(float) * (size_t)m * hidden);
+  L.off_staging = take(sizeof(float) * (size_t)L.max_tiles * TM * hidden);
+  L.cub_bytes = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, L.cub_bytes, (const int32_t*)nullptr, (int32_t*)nullptr, (int)(L.total + 1));
+  L.off_cub = take(L.cub_bytes + 256);
+  L.bytes = off;
+  return true;
+}
+
+extern "C" size_t gp_student_tc_workspace_bytes(const gp_student_desc* desc_host, int64_t m) {
+  TcLayout L;
+  if (!tc_layout(desc_host, m, L)) return 0;
+  return L.bytes;
+}
+
+// bf16 hi/lo K-major repack of every layer's weights: layer l at element offset sum_{j<l} kv*2*cout*cin
+extern "C" size_t gp_student_tc_pack_bytes(const gp_student_desc* d) {
+  if (!d || d->n_layers < 1 || d->n_layers > 16) return 0;
+  size_t n = 0;
+  for (int l = 0; l < d->n_layers; ++l) n += (size_t)d->kv[l] * 2 * d->cout[l] * d->cin[l];
+  return n * sizeof(__nv_bfloat16);
+}
+
+extern "C" int gp_student_tc_pack(const gp_student_desc* d, const float* weights, void* packed, gp_stream_t stream) {
+  GP_CHECK_ARG(d && d->n_layers >= 1 && d->n_layers <= 16, "gp_student_tc_pack: bad descriptor");
+  GP_CHECK_ARG(((uintptr_t)packed % 128) == 0, "gp_student_tc_pack: packed buffer must be 128-byte aligned");
+  size_t off = 0;
+  for (int l = 0; l < d->n_layers; ++l) {
+    GP_CHECK_ARG(d->cin[l] % BK == 0, "gp_student_tc_pack: layer %d cin must be a multiple of 16", l);
+    int64_t total = (int64_t)d->kv[l] * d->cout[l] * d->cin[l];
+    tc_pack_weights_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        weights + d->w_off[l], d->kv[l], d->cin[l], d->cout[l], d->cin[l], (__nv_bfloat16*)packed + off);
+    GP_LAUNCH_CHECK();
+    off += (size_t)total * 2;
+  }
+  return GP_OK;
+}
+
+template <int N>
+static int launch_gemm(const CUtensorMap& map, const GemmParams& P, int grid, cudaStream_t st) {
+  static bool configured = false;
+  if (!configured) {
+    GP_CUDA(cudaFuncSetAttribute(gather_gemm_tc_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 Smem<N>::TOTAL));
+    configured = true;
+  }
+  gather_gemm_tc_kernel<N><<<grid, NTHREADS, Smem<N>::TOTAL, st>>>(map, P);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weights, const void* packed,
+                                     const float* x, int64_t cin_stride, const int32_t* nbr27, int64_t m,
+                                     float* embed, int normalize, void* workspace, size_t workspace_bytes,
+                                     gp_stream_t stream) {
+  TcLayout L;
+  GP_CHECK_ARG(tc_layout(d, m, L),
+               "gp_student_forward_tc: needs 3^3 layers of one hidden width followed by a 1^3 output layer");
+  const int H = L.hidden, E = d->cout[d->n_layers - 1];
+  GP_CHECK_ARG(H == 512 || H == 256 || H == 128, "gp_student_forward_tc: hidden width %d not in {128,256,512}", H);
+  GP_CHECK_ARG(E == 128, "gp_student_forward_tc: embed width %d must be 128", E);
+  for (int l = 0; l < d->n_layers; ++l) {
+    GP_CHECK_ARG(d->cin[l] % BK == 0, "gp_student_forward_tc: layer %d cin %% 16", l);
+    GP_CHECK_ARG(d->residual_from[l] == -1 || d->residual_from[l] == l - 2,
+                 "gp_student_forward_tc: layer %d residual must come from layer l-2", l);
+    if (l > 0) GP_CHECK_ARG(d->cin[l] == d->cout[l - 1], "gp_student_forward_tc: layer %d cin != previous cout", l);
+  }
+  GP_CHECK_ARG(cin_stride >= d->cin[0], "gp_student_forward_tc: input stride %lld < padded cin %d",
+               (long long)cin_stride, d->cin[0]);
+  GP_CHECK_ARG(((uintptr_t)workspace % 1024) == 0 || m == 0, "gp_student_forward_tc: workspace must be 1 KiB aligned");
+  if (workspace_bytes < L.bytes) {
+    gp_set_error("gp_student_forward_tc: workspace %zu < %zu", workspace_bytes, L.bytes);
+    return GP_ERR_WORKSPACE;
+  }
+  GP_CHECK_ARG(encode_tiled_fn() != nullptr, "gp_student_forward_tc: cuTensorMapEncodeTiled unavailable");
+  if (m == 0) return GP_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  static int sm_count = 0;
+  if (!sm_count) {
+    int dev = 0;
+    GP_CUDA(cudaGetDevice(&dev));
+    GP_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+  }
+  char* ws = (char*)workspace;
+  int32_t* flags = (int32_t*)(ws + L.off_flags);
+  int32_t* pos = (int32_t*)(ws + L.off_pos);
+  int32_t* pair_in = (int32_t*)(ws + L.off_pair_in);
+  TileInfo* tiles = (TileInfo*)(ws + L.off_tiles);
+  int32_t* ntiles = (int32_t*)(ws + L.off_ntiles);
+  int32_t* gtile0 = (int32_t*)(ws + L.off_gtile0);
+  __nv_bfloat16* xin = (__nv_bfloat16*)(ws + L.off_xin);
+  float* staging = (float*)(ws + L.off_staging);
+
+  // pair lists + tile tables (shared by every 3^3 layer)
+  tc_pair_flags_kernel<<<(unsigned)((L.total + 1 + 255) / 256), 256, 0, st>>>(nbr27, m, L.S, L.total, flags);
+  GP_LAUNCH_CHECK();
+  size_t cb = L.cub_bytes + 256;
+  GP_CUDA(cub::DeviceScan::ExclusiveSum(ws + L.off_cub, cb, flags, pos, (int)(L.total + 1), st));
+  tc_pair_fill_kernel<<<(unsigned)((L.total + 255) / 256), 256, 0, st>>>(nbr27, pos, m, L.S, L.total, pair_in);
+  GP_LAUNCH_CHECK();
+  tc_build_tiles_kernel<<<L.nslab, 256, 0, st>>>(pos, L.S, L.max_tiles, tiles, ntiles, gtile0);
+  GP_LAUNCH_CHECK();
+  {
+    int64_t tot = m * L.kp0;
+    tc_split_input_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(x, cin_stride, d->cin[0], L.kp0, m, xin);
+    GP_LAUNCH_CHECK();
+  }
+
+  const __nv_bfloat16* in = xin;
+  int in_kp = L.kp0;
+  size_t woff = 0;  // element offset into `packed`
+  int act_i = 0, res_i = 0;
+  const float* res_src[16];
+  for (int l = 0; l < 16; ++l) res_src[l] = nullptr;
+  for (int l = 0; l + 1 < d->n_layers; ++l) {
+    CUtensorMap map;
+    const __nv_bfloat16* wl = (const __nv_bfloat16*)packed + woff;
+    GP_CHECK_ARG(make_weight_map(&map, wl, (int64_t)27 * 2 * H, in_kp, H < 256 ? H : 256),
+                 "gp_student_forward_tc: cuTensorMapEncodeTiled failed (layer %d)", l);
+    bool is_res_src = false;
+    for (int j = l + 1; j < d->n_layers; ++j) is_res_src |= d->residual_from[j] == l;
+    __nv_bfloat16* out_hilo = (__nv_bfloat16*)(ws + L.off_act[act_i]);
+    float* out_f32 = nullptr;
+    if (is_res_src) {
+      out_f32 = (float*)(ws + L.off_res[res_i]);
+      res_src[l] = out_f32;
+      res_i ^= 1;
+    }
+    const float* residual = d->residual_from[l] >= 0 ? res_src[d->residual_from[l]] : nullptr;
+    const float* sc = d->bn[l] ? weights + d->bn_off[l] : nullptr;
+    for (int slab = 0; slab < L.nslab; ++slab) {
+      GemmParams P;
+      P.a = in;
+      P.lda = 2 * (int64_t)in_kp;
+      P.kp = in_kp;
+      P.pair_in = pair_in;
+      P.tiles = tiles + (int64_t)slab * L.max_tiles;
+      P.ntiles_dev = ntiles + slab;
+      P.ntiles_host = 0;
+      P.m_rows = m;
+      P.cout_total = H;
+      P.c = staging;
+      P.ldc = H;
+      int rc = H == 512 ? launch_gemm<512>(map, P, sm_count, st)
+                        : (H == 256 ? launch_gemm<256>(map, P, sm_count, st) : launch_gemm<128>(map, P, sm_count, st));
+      if (rc) return rc;
+      int64_t rows = m - (int64_t)slab * L.S < L.S ? m - (int64_t)slab * L.S : L.S;
+      unsigned grid = (unsigned)((rows + 7) / 8);
+#define REDUCE(NV4)                                                                                              \
+  student_reduce_kernel<NV4><<<grid, 256, 0, st>>>(staging, nbr27, pos, gtile0, slab, L.S, m, sc, sc ? sc + H : nullptr, \
+                                                   residual, d->relu[l], out_hilo, out_f32)
+      if (H == 512) REDUCE(4);
+      else if (H == 256) REDUCE(2);
+      else REDUCE(1);
+#undef REDUCE
+      GP_LAUNCH_CHECK();
+    }
+    woff += (size_t)27 * 2 * H * in_kp;
+    in = out_hilo;
+    in_kp = H;
+    act_i = (act_i + 1) % 3;
+  }
+  {  // 1^3 output layer: plain GEMM [m, H] x [H, E] straight into `embed`
+    const int l = d->n_layers - 1;
+    CUtensorMap map;
+    GP_CHECK_ARG(make_weight_map(&map, (const __nv_bfloat16*)packed + woff, 2 * E, H, E),
+                 "gp_student_forward_tc: cuTensorMapEncodeTiled failed (output layer)");
+    GP_CHECK_ARG(!d->bn[l] && !d->relu[l] && d->residual_from[l] < 0, "gp_student_forward_tc: output layer is linear");
+    GemmParams P;
+    P.a = in;
+    P.lda = 2 * (int64_t)H;
+    P.kp = H;
+    P.pair_in = nullptr;
+    P.tiles = nullptr;
+    P.ntiles_dev = nullptr;
+    P.ntiles_host = (int)((m + TM - 1) / TM);
+    P.m_rows = m;
+    P.cout_total = E;
+    P.c = embed;
+    P.ldc = E;
+    int grid = P.ntiles_host < sm_count ? P.ntiles_host : sm_count;
+    int rc = launch_gemm<128>(map, P, grid, st);
+    if (rc) return rc;
+  }
+  if (normalize) {
+    int rc = gp_l2_normalize_rows(embed, m, E, st);
+    if (rc) return rc;
+  }
+  return GP_OK;
+}
