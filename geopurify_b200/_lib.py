@@ -51,6 +51,10 @@ _SIGS = {
     "gp_scatter_mean": (c_int, [_P, c_int64, c_int, _P, c_int64, c_int64, _P, c_int64, c_int, _P]),
     "gp_student_workspace_bytes": (c_size_t, [POINTER(StudentDesc), c_int64]),
     "gp_student_forward": (c_int, [POINTER(StudentDesc), _P, _P, c_int64, _P, c_int64, _P, c_int, _P, c_size_t, _P]),
+    "gp_student_tc_pack_bytes": (c_size_t, [POINTER(StudentDesc)]),
+    "gp_student_tc_pack": (c_int, [POINTER(StudentDesc), _P, _P, _P]),
+    "gp_student_tc_workspace_bytes": (c_size_t, [POINTER(StudentDesc), c_int64]),
+    "gp_student_forward_tc": (c_int, [POINTER(StudentDesc), _P, _P, _P, c_int64, _P, c_int64, _P, c_int, _P, c_size_t, _P]),
     "gp_affinity_softmax": (c_int, [_P, c_int, _P, c_int64, c_int, c_float, _P, _P]),
     "gp_pool": (c_int, [_P, c_int64, c_int, _P, _P, c_int64, c_int, c_int, _P, _P, POINTER(c_void_p), _P]),
     "gp_gather_rows": (c_int, [_P, c_int64, c_int, _P, c_int64, _P, _P]),

@@ -9,6 +9,7 @@
 #define GP_SM_COUNT 148
 
 void gp_set_error(const char* fmt, ...);
+int gp_l2_normalize_rows(float* x, int64_t rows, int E, cudaStream_t st);  // student.cu
 
 #define GP_CHECK_ARG(cond, ...)          \
   do {                                   \

@@ -210,6 +210,14 @@ __global__ void l2_normalize_kernel(float* __restrict__ x, int64_t rows, int E) 
   for (int c = lane; c < E; c += 32) x[r * E + c] *= inv;
 }
 
+// shared with student_tc.cu
+int gp_l2_normalize_rows(float* x, int64_t rows, int E, cudaStream_t st) {
+  if (rows == 0) return GP_OK;
+  l2_normalize_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(x, rows, E);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
 extern "C" int gp_student_forward(const gp_student_desc* d, const float* weights, const float* x, int64_t cin_stride,
                                   const int32_t* nbr27, int64_t m, float* embed, int normalize, void* workspace,
                                   size_t workspace_bytes, gp_stream_t stream) {

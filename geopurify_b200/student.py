@@ -79,6 +79,8 @@ class AffinityPredictor(nn.Module):
         self.res_blocks = nn.Sequential(*[MinkowskiResBlock(hidden_dim) for _ in range(4)])
         self.output_layer = SparseConvolution(hidden_dim, embed_dim, kernel_size=1, dimension=3)
         self._packed = None
+        self._packed_tc = None
+        self.precision = "bf16x3"   # "bf16x3": tcgen05 tensor cores, fp32-faithful split; "fp32": SIMT verification path
         self.eval()
 
     # -- reference API -------------------------------------------------------------------------
@@ -88,6 +90,7 @@ class AffinityPredictor(nn.Module):
 
     def load_state_dict(self, state_dict, strict=True, **kw):
         self._packed = None
+        self._packed_tc = None
         return super().load_state_dict(state_dict, strict=strict, **kw)
 
     @property
@@ -156,6 +159,22 @@ class AffinityPredictor(nn.Module):
         if x.stride(0) < self.input_stride:
             raise L.GeoPurifyError(f"student input rows need stride >= {self.input_stride} (zero padded)")
         embed = torch.empty((m, self.embed_dim), dtype=torch.float32, device=x.device)
+        if self.precision == "bf16x3":
+            if self._packed_tc is None or self._packed_tc.device != x.device:
+                nbp = lib.gp_student_tc_pack_bytes(ctypes.byref(desc))
+                self._packed_tc = torch.empty(nbp, dtype=torch.uint8, device=x.device)
+                L.check(lib.gp_student_tc_pack(ctypes.byref(desc), L.ptr(flat), L.ptr(self._packed_tc), L.stream()))
+                L.count(desc.n_layers)
+            nb = lib.gp_student_tc_workspace_bytes(ctypes.byref(desc), m)
+            if nb == 0:
+                raise L.GeoPurifyError("student: layer structure not supported by the tensor-core path")
+            ws = torch.empty(nb, dtype=torch.uint8, device=x.device)
+            L.check(lib.gp_student_forward_tc(ctypes.byref(desc), L.ptr(flat), L.ptr(self._packed_tc), L.ptr(x),
+                                              x.stride(0), L.ptr(nbr27), m, L.ptr(embed), int(normalize), L.ptr(ws),
+                                              nb, L.stream()))
+            nslab = (m + 32767) // 32768
+            L.count(6 + 2 * nslab * (desc.n_layers - 1) + 2)
+            return embed
         nb = lib.gp_student_workspace_bytes(ctypes.byref(desc), m)
         ws = torch.empty(max(nb, 256), dtype=torch.uint8, device=x.device)
         L.check(lib.gp_student_forward(ctypes.byref(desc), L.ptr(flat), L.ptr(x), x.stride(0), L.ptr(nbr27), m,

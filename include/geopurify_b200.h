@@ -152,6 +152,18 @@ int gp_student_forward(const gp_student_desc* desc_host, const float* weights, c
                        const int32_t* nbr27, int64_t m, float* embed, int normalize, void* workspace,
                        size_t workspace_bytes, gp_stream_t stream);
 
+/* ---- A8 on the tensor cores (tcgen05 + TMEM, sm_100a): same contract as gp_student_forward, fp32-faithful through a
+ * bf16 hi/lo split of activations and weights (3 MMAs per product term, fp32 accumulate in TMEM).
+ *   packed    bf16 K-major repack of the conv weights made once by gp_student_tc_pack (128-byte aligned)
+ *   weights   the same float32 buffer as gp_student_forward (the folded BN scale/shift are read from it)
+ *   workspace 1 KiB aligned */
+size_t gp_student_tc_pack_bytes(const gp_student_desc* desc_host);
+int gp_student_tc_pack(const gp_student_desc* desc_host, const float* weights, void* packed, gp_stream_t stream);
+size_t gp_student_tc_workspace_bytes(const gp_student_desc* desc_host, int64_t m);
+int gp_student_forward_tc(const gp_student_desc* desc_host, const float* weights, const void* packed, const float* x,
+                          int64_t cin_stride, const int32_t* nbr27, int64_t m, float* embed, int normalize,
+                          void* workspace, size_t workspace_bytes, gp_stream_t stream);
+
 /* ---- A10: w[s,k] = softmax_k(sharpen * <e_s, e_nbr(s,k)>) (models/affinity_module.py:1559-1572). */
 int gp_affinity_softmax(const float* embed, int E, const int32_t* nbr_sorted, int64_t m, int K, float sharpen,
                         float* weights, gp_stream_t stream);

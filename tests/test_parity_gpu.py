@@ -231,3 +231,20 @@ def test_scene_labels_histograms_miou(scene_run):
     assert (h[2] == ref["target"].numpy()).all()
     from geopurify_b200.validation import mean_iou
     assert mean_iou(h[0], h[1], h[2]) == oracle.miou(ref["inter"].numpy(), ref["union"].numpy(), ref["target"].numpy())
+
+
+def test_student_tensor_core_vs_simt_vs_oracle(scene_run):
+    """The tcgen05 bf16x3 path and the fp32 SIMT verification path against the oracle's fp32 forward."""
+    model, ref = scene_run["model"], scene_run["ref"]
+    st = model.affinity_student
+    vin, nbr27 = model.last["voxel_in"], model.last["nbr27"]
+    order = model.last["index"].order.long().cpu()
+    errs = {}
+    for prec in ("bf16x3", "fp32"):
+        st.precision = prec
+        emb = st.forward_sorted(vin, nbr27, normalize=True)
+        torch.cuda.synchronize()
+        errs[prec] = (emb.cpu() - ref["embed"][order]).abs().max().item()
+    st.precision = "bf16x3"
+    print("student max-abs vs oracle:", errs)
+    assert errs["fp32"] < 2e-5 and errs["bf16x3"] < 2e-4, errs
