@@ -98,15 +98,14 @@ __device__ __forceinline__ void nn1_cell_of(const Nn1Header* h, float x, float y
 
 __global__ void nn1_keys_kernel(const float* __restrict__ xyz, const uint8_t* __restrict__ seen, int64_t n,
                                 const Nn1Header* __restrict__ h, uint32_t* __restrict__ keys,
-                                int32_t* __restrict__ vals) {
+                                int32_t* __restrict__ vals, int32_t* __restrict__ nn) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  uint32_t key = 0x3fffffu;  // unseen points sort to the end
-  if (seen[i]) {
-    int cx, cy, cz;
-    nn1_cell_of(h, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], cx, cy, cz);
-    key = (uint32_t)((cz * NN1_MAX_DIM + cy) * NN1_MAX_DIM + cx);
-  }
+  int cx, cy, cz;
+  nn1_cell_of(h, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], cx, cy, cz);
+  uint32_t key = (uint32_t)((cz * NN1_MAX_DIM + cy) * NN1_MAX_DIM + cx);
+  if (seen[i]) nn[i] = (int32_t)i;
+  else key |= 1u << 21;  // unseen points sort after every seen one, in cell order
   keys[i] = key;
   vals[i] = (int32_t)i;
 }
@@ -117,27 +116,60 @@ __global__ void nn1_cells_kernel(const float* __restrict__ xyz, const uint32_t* 
   int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n) return;
   uint32_t k = keys_sorted[s];
-  if (k == 0x3fffffu) return;
+  if (k >> 21) return;
   int i = vals_sorted[s];
   sorted[s] = make_float4(xyz[3 * (int64_t)i], xyz[3 * (int64_t)i + 1], xyz[3 * (int64_t)i + 2], __int_as_float(i));
   if (s == 0 || keys_sorted[s - 1] != k) cells[k].x = (int)s;
   if (s == n - 1 || keys_sorted[s + 1] != k) cells[k].y = (int)s + 1;
 }
 
-// one thread per point; unseen points search outward ring by ring.  Distances in float64 on the float32
-// coordinates (as the KD-tree does), ties -> lowest index.
-__global__ void __launch_bounds__(128) nn1_query_kernel(const float* __restrict__ xyz,
-                                                         const uint8_t* __restrict__ seen, int64_t n,
+// One warp per unseen point.  Unseen points carry sort keys (1 << 21 | own cell), so they sit at the tail of the
+// sorted arrays in cell order (neighbouring warps search neighbouring cells); warp w takes sorted position n-1-w and
+// quits when it reaches a seen point.  Lanes enumerate the cells of Chebyshev shell r in parallel, each lane scans
+// its cell's members; distances in float64 on the float32 coordinates (as the KD-tree does), ties -> lowest index.
+__device__ __forceinline__ bool shell_cell(int r, int t, int& dx, int& dy, int& dz) {
+  if (r == 0) {
+    dx = dy = dz = 0;
+    return t == 0;
+  }
+  const int w = 2 * r + 1, face = w * w, ring = 8 * r;
+  if (t < face) {
+    dz = -r;
+    dx = t % w - r;
+    dy = t / w - r;
+    return true;
+  }
+  t -= face;
+  if (t < (w - 2) * ring) {
+    dz = t / ring - r + 1;
+    int u = t % ring, side = u / (2 * r), j = u % (2 * r);
+    dx = side == 0 ? -r + j : (side == 1 ? r : (side == 2 ? r - j : -r));
+    dy = side == 0 ? -r : (side == 1 ? -r + j : (side == 2 ? r : r - j));
+    return true;
+  }
+  t -= (w - 2) * ring;
+  if (t < face) {
+    dz = r;
+    dx = t % w - r;
+    dy = t / w - r;
+    return true;
+  }
+  return false;
+}
+
+__global__ void __launch_bounds__(256) nn1_query_kernel(const float* __restrict__ xyz, int64_t n,
                                                          const Nn1Header* __restrict__ h,
+                                                         const uint32_t* __restrict__ keys_sorted,
+                                                         const int32_t* __restrict__ vals_sorted,
                                                          const float4* __restrict__ sorted,
                                                          const int2* __restrict__ cells, int32_t* __restrict__ nn) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  if (seen[i]) {
-    nn[i] = (int32_t)i;
-    return;
-  }
-  const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+  const int lane = threadIdx.x & 31;
+  const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (w >= n) return;
+  const int64_t spos = n - 1 - w;
+  if ((keys_sorted[spos] >> 21) == 0) return;  // a seen point: every later warp is seen as well
+  const int i = vals_sorted[spos];
+  const float x = xyz[3 * (int64_t)i], y = xyz[3 * (int64_t)i + 1], z = xyz[3 * (int64_t)i + 2];
   int qx, qy, qz;
   nn1_cell_of(h, x, y, z, qx, qy, qz);
   const int dx_ = h->dim[0], dy_ = h->dim[1], dz_ = h->dim[2];
@@ -147,38 +179,42 @@ __global__ void __launch_bounds__(128) nn1_query_kernel(const float* __restrict_
   double fx = ((double)x - (double)h->mn[0]) / cell - qx, fy = ((double)y - (double)h->mn[1]) / cell - qy,
          fz = ((double)z - (double)h->mn[2]) / cell - qz;
   double slack = fmin(fmin(fmin(fx, 1.0 - fx), fmin(fy, 1.0 - fy)), fmin(fz, 1.0 - fz));
-  // minus an absolute margin that covers float rounding of the cell assignment
-  slack = fmax(0.0, fmin(slack, 1.0) - 1e-3) * cell;
+  slack = fmax(0.0, fmin(slack, 1.0) - 1e-3) * cell;  // margin for float rounding of the cell assignment
   double best = 1e300;
-  int besti = -1;
+  int besti = 0x7fffffff;
   for (int r = 0; r <= rmax; ++r) {
-    int z0 = max(qz - r, 0), z1 = min(qz + r, dz_ - 1);
-    int y0 = max(qy - r, 0), y1 = min(qy + r, dy_ - 1);
-    int x0 = max(qx - r, 0), x1 = min(qx + r, dx_ - 1);
-    for (int cz = z0; cz <= z1; ++cz)
-      for (int cy = y0; cy <= y1; ++cy) {
-        bool face = (abs(cz - qz) == r) || (abs(cy - qy) == r);
-        int step = face ? 1 : max(1, 2 * r);  // interior rows: only the two end cells are on the shell
-        for (int cx = face ? x0 : (qx - r); cx <= x1; cx += step) {
-          if (cx < x0) continue;
-          if (!face && abs(cx - qx) != r) continue;
-          int2 ce = __ldg(&cells[(cz * NN1_MAX_DIM + cy) * NN1_MAX_DIM + cx]);
-          for (int j = ce.x; j < ce.y; ++j) {
-            float4 p = __ldg(&sorted[j]);
-            double ddx = (double)p.x - (double)x, ddy = (double)p.y - (double)y, ddz = (double)p.z - (double)z;
-            double d2 = ddx * ddx + ddy * ddy + ddz * ddz;
-            int pi = __float_as_int(p.w);
-            if (d2 < best || (d2 == best && pi < besti)) {
-              best = d2;
-              besti = pi;
-            }
-          }
+    const int wd = 2 * r + 1;
+    const int total = r == 0 ? 1 : 2 * wd * wd + (wd - 2) * 8 * r;
+    for (int t = lane; t < total; t += 32) {
+      int ddx, ddy, ddz;
+      if (!shell_cell(r, t, ddx, ddy, ddz)) continue;
+      int cx = qx + ddx, cy = qy + ddy, cz = qz + ddz;
+      if (cx < 0 || cy < 0 || cz < 0 || cx >= dx_ || cy >= dy_ || cz >= dz_) continue;
+      int2 ce = __ldg(&cells[(cz * NN1_MAX_DIM + cy) * NN1_MAX_DIM + cx]);
+      for (int j = ce.x; j < ce.y; ++j) {
+        float4 p = __ldg(&sorted[j]);
+        double ex = (double)p.x - (double)x, ey = (double)p.y - (double)y, ez = (double)p.z - (double)z;
+        double d2 = ex * ex + ey * ey + ez * ez;
+        int pi = __float_as_int(p.w);
+        if (d2 < best || (d2 == best && pi < besti)) {
+          best = d2;
+          besti = pi;
         }
       }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      double ob = __shfl_xor_sync(0xffffffffu, best, o);
+      int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+      if (ob < best || (ob == best && oi < besti)) {
+        best = ob;
+        besti = oi;
+      }
+    }
     double g = fmax(0.0, r * cell + slack - 1e-3 * cell * (r > 0));
-    if (besti >= 0 && best <= g * g) break;
+    if (besti != 0x7fffffff && best <= g * g) break;
   }
-  nn[i] = besti;
+  if (lane == 0) nn[i] = besti == 0x7fffffff ? -1 : besti;
 }
 
 extern "C" size_t gp_nn1_fill_workspace_bytes(int64_t n) {
@@ -212,13 +248,13 @@ extern "C" int gp_nn1_fill(const float* xyz, int64_t n, const uint8_t* seen, flo
   uint32_t* kout = (uint32_t*)(ws + L.off_kout);
   int32_t* vin = (int32_t*)(ws + L.off_vin);
   int32_t* vout = (int32_t*)(ws + L.off_vout);
-  nn1_keys_kernel<<<grid, 256, 0, st>>>(xyz, seen, n, h, kin, vin);
+  nn1_keys_kernel<<<grid, 256, 0, st>>>(xyz, seen, n, h, kin, vin, nn);
   GP_LAUNCH_CHECK();
   size_t cb = L.cub_bytes + 256;
   GP_CUDA(cub::DeviceRadixSort::SortPairs(ws + L.off_cub, cb, kin, kout, vin, vout, (int)n, 0, 22, st));
   nn1_cells_kernel<<<grid, 256, 0, st>>>(xyz, kout, vout, n, (float4*)(ws + L.off_sorted), cells);
-  nn1_query_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(xyz, seen, n, h, (const float4*)(ws + L.off_sorted),
-                                                               cells, nn);
+  nn1_query_kernel<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(xyz, n, h, kout, vout, (const float4*)(ws + L.off_sorted),
+                                                           cells, nn);
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

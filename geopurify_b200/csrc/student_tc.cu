@@ -560,7 +560,7 @@ extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weig
   }
   GP_CHECK_ARG(cin_stride >= d->cin[0], "gp_student_forward_tc: input stride %lld < padded cin %d",
                (long long)cin_stride, d->cin[0]);
-  GP_CHECK_ARG(((uintptr_t)workspace % 1024) == 0 || m == 0, "gp_student_forward_tc: workspace must be 1 KiB aligned");
+  GP_CHECK_ARG(((uintptr_t)workspace % 256) == 0 || m == 0, "gp_student_forward_tc: workspace must be 256-byte aligned");
   if (workspace_bytes < L.bytes) {
     gp_set_error("gp_student_forward_tc: workspace %zu < %zu", workspace_bytes, L.bytes);
     return GP_ERR_WORKSPACE;

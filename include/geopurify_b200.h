@@ -156,7 +156,7 @@ int gp_student_forward(const gp_student_desc* desc_host, const float* weights, c
  * bf16 hi/lo split of activations and weights (3 MMAs per product term, fp32 accumulate in TMEM).
  *   packed    bf16 K-major repack of the conv weights made once by gp_student_tc_pack (128-byte aligned)
  *   weights   the same float32 buffer as gp_student_forward (the folded BN scale/shift are read from it)
- *   workspace 1 KiB aligned */
+ *   workspace 256-byte aligned */
 size_t gp_student_tc_pack_bytes(const gp_student_desc* desc_host);
 int gp_student_tc_pack(const gp_student_desc* desc_host, const float* weights, void* packed, gp_stream_t stream);
 size_t gp_student_tc_workspace_bytes(const gp_student_desc* desc_host, int64_t m);
