@@ -57,6 +57,10 @@ _SIGS = {
     "gp_student_forward_tc": (c_int, [POINTER(StudentDesc), _P, _P, _P, c_int64, _P, c_int64, _P, c_int, _P, c_size_t, _P]),
     "gp_affinity_softmax": (c_int, [_P, c_int, _P, c_int64, c_int, c_float, _P, _P]),
     "gp_pool": (c_int, [_P, c_int64, c_int, _P, _P, c_int64, c_int, c_int, _P, _P, POINTER(c_void_p), _P]),
+    "gp_pool_plan_bytes": (c_size_t, [c_int64, c_int]),
+    "gp_pool_plan": (c_int, [_P, _P, c_int64, c_int, _P, c_size_t, _P]),
+    "gp_pool_tc_workspace_bytes": (c_size_t, [c_int64]),
+    "gp_pool_tc": (c_int, [_P, c_int64, c_int, _P, _P, _P, c_int64, c_int, c_int, _P, _P, c_size_t, _P]),
     "gp_gather_rows": (c_int, [_P, c_int64, c_int, _P, c_int64, _P, _P]),
     "gp_logits_workspace_bytes": (c_size_t, [c_int, c_int]),
     "gp_logits_argmax": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, c_float, _P, _P, _P, _P, c_size_t, _P]),

@@ -1,0 +1,463 @@
+// Geometry-Guided Pooling on the tensor cores: F <- A F as a block-local dense GEMM (tcgen05 + TMEM, bf16x3 split).
+// Replaces the cuSPARSE SpMM loop of the reference (models/affinity_module.py:1575-1587).
+//
+// In Morton order the K-neighbour lists of consecutive voxels overlap heavily: 128 consecutive voxels reference only
+// ~5 |tile| distinct rows instead of 128 K.  A per-scene PLAN stores, for every tile of 128 output voxels, the sorted
+// union U of its neighbour lists and the dense 128 x |U| weight block (zeros where a voxel does not use a neighbour),
+// already split into bf16 hi/lo and laid out K-step by K-step in the shared-memory operand layout.  One application is
+//   out_tile[128 x D] = W_tile[128 x |U|] * F[U, :]                     (one 128 x 512 fp32 accumulator in TMEM)
+// with the rows F[U] gathered ONCE per tile by cp.async into the MN-major operand layout -- the gathered bytes drop
+// from K rows per voxel (through L1) to |U|/128 rows per voxel (through L2), and the 128 x 512 accumulators that no
+// register file can hold live in TMEM.  F travels between applications as bf16 hi/lo planes (16 mantissa bits,
+// relative error 2^-17 per application); products use Whi*Fhi + Whi*Flo + Wlo*Fhi with fp32 accumulation.
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace {
+
+constexpr int PT = 128;          // output voxels per tile = UMMA M = TMEM lanes
+constexpr int PD = 512;          // feature width = TMEM columns
+constexpr int PK = 16;           // union rows per K-step = UMMA K (bf16)
+constexpr int KSTEP_CAP = 128;   // K-steps a tile may use (2048 union rows); larger unions take the row-wise path
+constexpr int A_STEP = 2 * PT * PK * 2;  // bytes of W (hi + lo) per K-step: 8 KB
+constexpr int B_PLANE = PK * PD * 2;     // bytes of one plane of gathered rows per K-step: 16 KB
+constexpr int PSTAGE = A_STEP + 2 * B_PLANE;  // 40 KB
+constexpr int PNSTAGE = 5;
+constexpr int PLAG = 2;
+constexpr int P_EPI_LD = 36;
+constexpr int PTHREADS = 384;    // warp 0 W bulk copies, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue, 8-11 row gather
+constexpr int PSMEM = PNSTAGE * PSTAGE + 4 * 32 * P_EPI_LD * 4 + 256 + 1024;
+
+struct PlanLayout {
+  int64_t tiles;
+  size_t off_count, off_uidx, off_w, bytes;
+};
+
+inline PlanLayout plan_layout(int64_t m) {
+  PlanLayout L;
+  L.tiles = (m + PT - 1) / PT;
+  size_t off = 0;
+  auto take = [&](size_t b) {
+    size_t o = off;
+    off += gp_align_up(b, 1024);
+    return o;
+  };
+  L.off_count = take(sizeof(int32_t) * L.tiles);
+  L.off_uidx = take(sizeof(int32_t) * L.tiles * KSTEP_CAP * PK);
+  L.off_w = take((size_t)L.tiles * KSTEP_CAP * A_STEP);
+  L.bytes = off;
+  return L;
+}
+
+__device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+  hi = __float2bfloat16_rn(v);
+  lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+}
+
+// ------------------------------------------------------------------ plan: one CTA per tile
+// dynamic smem: keys[npow2] (sorted in place; the unique prefix is then compacted into the same array)
+__global__ void __launch_bounds__(256) pool_tc_plan_kernel(const int32_t* __restrict__ nbr,
+                                                            const float* __restrict__ w, int64_t m, int K, int npow2,
+                                                            int32_t* __restrict__ ucount, int32_t* __restrict__ uidx,
+                                                            uint8_t* __restrict__ wplan) {
+  extern __shared__ uint32_t keys[];
+  __shared__ int s_warp_cnt[8];
+  const int64_t t = blockIdx.x;
+  const int64_t row0 = t * PT;
+  const int rows = (int)min((int64_t)PT, m - row0);
+  const int nent = rows * K;
+  for (int e = threadIdx.x; e < npow2; e += 256) keys[e] = e < nent ? (uint32_t)__ldg(nbr + row0 * K + e) : 0xffffffffu;
+  __syncthreads();
+  for (int k = 2; k <= npow2; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < (npow2 >> 1); i += 256) {
+        int lo = ((i & ~(j - 1)) << 1) | (i & (j - 1));
+        int hi = lo | j;
+        uint32_t a = keys[lo], b = keys[hi];
+        bool up = (lo & k) == 0;
+        if ((a > b) == up) {
+          keys[lo] = b;
+          keys[hi] = a;
+        }
+      }
+      __syncthreads();
+    }
+  // unique, in place: chunks of 256 entries; positions never overtake the read cursor
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  int nu = 0;
+  for (int e0 = 0; e0 < nent; e0 += 256) {
+    int e = e0 + threadIdx.x;
+    uint32_t v = e < nent ? keys[e] : 0xffffffffu;
+    bool first = e < nent && (e == 0 || keys[e - 1] != v);
+    unsigned bal = __ballot_sync(0xffffffffu, first);
+    if (lane == 0) s_warp_cnt[wp] = __popc(bal);
+    __syncthreads();
+    int base = nu;
+    for (int i = 0; i < wp; ++i) base += s_warp_cnt[i];
+    int tot = 0;
+    for (int i = 0; i < 8; ++i) tot += s_warp_cnt[i];
+    if (first) keys[base + __popc(bal & ((1u << lane) - 1))] = v;
+    nu += tot;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) ucount[t] = nu;
+  const int ksteps = (nu + PK - 1) / PK;
+  if (ksteps > KSTEP_CAP) return;  // this tile is served by the row-wise kernel
+  int32_t* ui = uidx + t * (int64_t)(KSTEP_CAP * PK);
+  for (int e = threadIdx.x; e < ksteps * PK; e += 256) ui[e] = (int32_t)keys[e < nu ? e : nu - 1];  // pad: weight 0
+  uint8_t* wp_base = wplan + (size_t)t * KSTEP_CAP * A_STEP;
+  for (int e = threadIdx.x; e < ksteps * (A_STEP / 16); e += 256) ((uint4*)wp_base)[e] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  for (int e = threadIdx.x; e < nent; e += 256) {
+    uint32_t v = (uint32_t)__ldg(nbr + row0 * K + e);
+    int lo = 0, hi = nu - 1;
+    while (lo < hi) {
+      int mid = (lo + hi) >> 1;
+      if (keys[mid] < v) lo = mid + 1;
+      else hi = mid;
+    }
+    const int r = e / K, ks = lo >> 4, kk = lo & 15;
+    __nv_bfloat16 h, l;
+    split_bf16(__ldg(w + row0 * K + e), h, l);
+    // K-major, 32-byte rows, SWIZZLE_32B: 16-byte chunk c of row r is stored at chunk c ^ ((r >> 2) & 1)
+    uint8_t* p = wp_base + (size_t)ks * A_STEP + r * 32 + ((((kk >> 3) ^ ((r >> 2) & 1))) << 4) + (kk & 7) * 2;
+    *(__nv_bfloat16*)p = h;
+    *(__nv_bfloat16*)(p + PT * PK * 2) = l;
+  }
+}
+
+// fp32 rows -> bf16 hi/lo planes [m][2][PD]
+__global__ void pool_tc_split_kernel(const float* __restrict__ f, int64_t stride, int64_t m,
+                                     __nv_bfloat16* __restrict__ planes) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= m * (PD / 4)) return;
+  int64_t r = t / (PD / 4);
+  int c = (int)(t - r * (PD / 4)) * 4;
+  float4 v = *(const float4*)(f + r * stride + c);
+  __nv_bfloat16 h[4], l[4];
+  split_bf16(v.x, h[0], l[0]);
+  split_bf16(v.y, h[1], l[1]);
+  split_bf16(v.z, h[2], l[2]);
+  split_bf16(v.w, h[3], l[3]);
+  *(uint2*)(planes + r * 2 * PD + c) = *(const uint2*)h;
+  *(uint2*)(planes + r * 2 * PD + PD + c) = *(const uint2*)l;
+}
+
+
+// ------------------------------------------------------------------ one application: out = W_plan * F[U]
+struct PoolParams {
+  const __nv_bfloat16* fin;   // [m][2][PD] hi | lo planes
+  const int32_t* ucount;      // [tiles]
+  const int32_t* uidx;        // [tiles][KSTEP_CAP * PK]
+  const uint8_t* wplan;       // [tiles][KSTEP_CAP][A_STEP]
+  int64_t m;
+  int tiles;
+  __nv_bfloat16* out_planes;  // next application's input, or nullptr
+  float* out_f32;             // [m][PD] final result, or nullptr
+};
+
+__global__ void __launch_bounds__(PTHREADS, 1) pool_tc_kernel(const PoolParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  float* epi = (float*)(smem + PNSTAGE * PSTAGE);
+  uint64_t* bars = (uint64_t*)(smem + PNSTAGE * PSTAGE + 4 * 32 * P_EPI_LD * 4);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + PNSTAGE;
+  uint64_t* tmem_full = bars + 2 * PNSTAGE;
+  uint64_t* tmem_empty = tmem_full + 1;
+  uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < PNSTAGE; ++s) {
+      tc::mbar_init(&full[s], 4 + 1);  // 4 gather warps + the bulk-copy thread's expect_tx arrive
+      tc::mbar_init(&empty[s], 1);
+    }
+    tc::mbar_init(tmem_full, 1);
+    tc::mbar_init(tmem_empty, 4);
+    tc::fence_barrier_init();
+  }
+  if (warp == 2) tc::tmem_alloc<PD>(tmem_slot);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  auto ksteps_of = [&](int t) -> int {
+    int ks = (__ldg(P.ucount + t) + PK - 1) / PK;
+    return ks > KSTEP_CAP ? 0 : ks;  // overflow tiles are skipped here (row-wise kernel)
+  };
+
+  if (warp == 0) {
+    // ===================== W blocks: one 8 KB bulk copy per K-step =====================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < P.tiles; t += gridDim.x) {
+        const int ks_n = ksteps_of(t);
+        const uint8_t* src = P.wplan + (size_t)t * KSTEP_CAP * A_STEP;
+        for (int ks = 0; ks < ks_n; ++ks, ++it) {
+          const int s = it % PNSTAGE;
+          tc::mbar_wait(&empty[s], ((it / PNSTAGE) & 1) ^ 1);
+          tc::mbar_arrive_expect_tx(&full[s], A_STEP);
+          tc::bulk_load(tc::smem_u32(smem + s * PSTAGE), src + (size_t)ks * A_STEP, A_STEP, &full[s]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint64_t ADESC = tc::umma_desc_kmajor_base<32>();
+    constexpr uint64_t BDESC = tc::umma_desc_mnmajor_sw128_base(2048, 1024);
+    constexpr uint32_t IDESC = tc::umma_idesc_bf16(PT, 256, true);
+    uint32_t it = 0, tcount = 0;
+    for (int t = blockIdx.x; t < P.tiles; t += gridDim.x) {
+      const int ks_n = ksteps_of(t);
+      if (ks_n == 0) continue;
+      tc::mbar_wait(tmem_empty, (tcount & 1) ^ 1);
+      tc::tc_fence_after();
+      for (int ks = 0; ks < ks_n; ++ks, ++it) {
+        const int s = it % PNSTAGE;
+        tc::mbar_wait(&full[s], (it / PNSTAGE) & 1);
+        tc::tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_hi = tc::smem_u32(smem + s * PSTAGE);
+          const uint32_t a_lo = a_hi + PT * PK * 2;
+          const uint32_t b_hi = a_hi + A_STEP;
+          const uint32_t b_lo = b_hi + B_PLANE;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const uint32_t d = tmem_base + h * 256;
+            const uint32_t boff = h * (B_PLANE / 2);
+            tc::umma_bf16(d, tc::umma_desc(ADESC, a_lo), tc::umma_desc(BDESC, b_hi + boff), IDESC, ks > 0);
+            tc::umma_bf16(d, tc::umma_desc(ADESC, a_hi), tc::umma_desc(BDESC, b_lo + boff), IDESC, 1);
+            tc::umma_bf16(d, tc::umma_desc(ADESC, a_hi), tc::umma_desc(BDESC, b_hi + boff), IDESC, 1);
+          }
+          tc::umma_commit(&empty[s]);
+          if (ks == ks_n - 1) tc::umma_commit(tmem_full);
+        }
+        __syncwarp();
+      }
+      ++tcount;
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ===================== epilogue =====================
+    const int q = warp & 3;
+    float* buf = epi + q * 32 * P_EPI_LD;
+    uint32_t tcount = 0;
+    for (int t = blockIdx.x; t < P.tiles; t += gridDim.x) {
+      if (ksteps_of(t) == 0) continue;
+      tc::mbar_wait(tmem_full, tcount & 1);
+      tc::tc_fence_after();
+      const int64_t row_base = (int64_t)t * PT + q * 32;
+      const int rows_here = (int)min((int64_t)32, P.m - row_base);
+      for (int ch = 0; ch < PD / 32; ++ch) {
+        uint32_t v[32];
+        tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ch * 32, v);
+        tc::tmem_ld_wait();
+        if (ch == PD / 32 - 1) {
+          tc::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(tmem_empty);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *(float4*)(buf + lane * P_EPI_LD + j * 4) =
+              make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                          __uint_as_float(v[4 * j + 3]));
+        __syncwarp();
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr) {
+          const int row = rr * 4 + (lane >> 3), c4 = lane & 7;
+          if (row < rows_here) {
+            float4 o = *(const float4*)(buf + row * P_EPI_LD + c4 * 4);
+            const int col = ch * 32 + c4 * 4;
+            if (P.out_f32) *(float4*)(P.out_f32 + (row_base + row) * PD + col) = o;
+            if (P.out_planes) {
+              __nv_bfloat16 h[4], l[4];
+              split_bf16(o.x, h[0], l[0]);
+              split_bf16(o.y, h[1], l[1]);
+              split_bf16(o.z, h[2], l[2]);
+              split_bf16(o.w, h[3], l[3]);
+              __nv_bfloat16* dst = P.out_planes + (row_base + row) * 2 * PD + col;
+              *(uint2*)dst = *(const uint2*)h;
+              *(uint2*)(dst + PD) = *(const uint2*)l;
+            }
+          }
+        }
+        __syncwarp();
+      }
+      ++tcount;
+    }
+  } else if (warp >= 8) {
+    // ===================== gather of the union rows into the MN-major operand layout =====================
+    // thread r: union row k = r >> 3 of the K-step, 64-column block nb = r & 7 (128 contiguous bytes per plane)
+    const int r = threadIdx.x - 256;
+    const int k = r >> 3, nb = r & 7;
+    // atom (nb, k >> 3) at ((nb * 2 + (k >> 3)) * 1024), row (k & 7) of 128 bytes, 16-byte chunk c at c ^ (k & 7)
+    const uint32_t dst_off = A_STEP + (nb * 2 + (k >> 3)) * 1024 + (k & 7) * 128;
+    const uint32_t sw = k & 7;
+    uint32_t it = 0, signalled = 0;
+    for (int t = blockIdx.x; t < P.tiles; t += gridDim.x) {
+      const int ks_n = ksteps_of(t);
+      const int32_t* ui = P.uidx + (int64_t)t * (KSTEP_CAP * PK);
+      for (int ks = 0; ks < ks_n; ++ks, ++it) {
+        const int s = it % PNSTAGE;
+        const int u = __ldg(ui + ks * PK + k);
+        tc::mbar_wait(&empty[s], ((it / PNSTAGE) & 1) ^ 1);
+        const __nv_bfloat16* src = P.fin + (int64_t)u * 2 * PD + nb * 64;
+        const uint32_t dst = tc::smem_u32(smem + s * PSTAGE) + dst_off;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          tc::cp_async16(dst + ((c ^ sw) << 4), src + c * 8, 16);
+          tc::cp_async16(dst + B_PLANE + ((c ^ sw) << 4), src + PD + c * 8, 16);
+        }
+        tc::cp_async_commit();
+        if (it >= PLAG) {
+          tc::cp_async_wait<PLAG>();
+          tc::fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(&full[signalled % PNSTAGE]);
+          ++signalled;
+        }
+      }
+    }
+    tc::cp_async_wait<0>();
+    tc::fence_proxy_async();
+    __syncwarp();
+    for (; signalled < it; ++signalled)
+      if (lane == 0) tc::mbar_arrive(&full[signalled % PNSTAGE]);
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc<PD>(tmem_base);
+}
+
+// tiles whose union exceeds KSTEP_CAP K-steps: one warp per output row straight from the neighbour lists
+__global__ void __launch_bounds__(256) pool_rows_planes_kernel(const __nv_bfloat16* __restrict__ fin,
+                                                                const int32_t* __restrict__ ucount,
+                                                                const int32_t* __restrict__ nbr,
+                                                                const float* __restrict__ w, int64_t m, int K,
+                                                                __nv_bfloat16* __restrict__ out_planes,
+                                                                float* __restrict__ out_f32) {
+  const int t = blockIdx.x;
+  if ((__ldg(ucount + t) + PK - 1) / PK <= KSTEP_CAP) return;
+  const int lane = threadIdx.x & 31;
+  for (int rr = threadIdx.x >> 5; rr < PT; rr += 8) {
+    const int64_t s = (int64_t)t * PT + rr;
+    if (s >= m) break;
+    float acc[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+    for (int k = 0; k < K; ++k) {
+      const int u = __ldg(nbr + s * K + k);
+      const float wk = __ldg(w + s * K + k);
+      const __nv_bfloat16* row = fin + (int64_t)u * 2 * PD;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        int c = j * 32 + lane;
+        acc[j] = fmaf(wk, __bfloat162float(row[c]) + __bfloat162float(row[PD + c]), acc[j]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      int c = j * 32 + lane;
+      if (out_f32) out_f32[s * PD + c] = acc[j];
+      if (out_planes) {
+        __nv_bfloat16 h, l;
+        split_bf16(acc[j], h, l);
+        out_planes[s * 2 * PD + c] = h;
+        out_planes[s * 2 * PD + PD + c] = l;
+      }
+    }
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ host side
+extern "C" size_t gp_pool_plan_bytes(int64_t m, int K) {
+  if (m < 0 || K < 1 || K > 128) return 0;
+  return plan_layout(m).bytes;
+}
+
+extern "C" int gp_pool_plan(const int32_t* nbr_sorted, const float* weights, int64_t m, int K, void* plan,
+                            size_t plan_bytes, gp_stream_t stream) {
+  GP_CHECK_ARG(m >= 0 && K >= 1 && K <= 128, "gp_pool_plan: bad sizes");
+  GP_CHECK_ARG(((uintptr_t)plan % 256) == 0, "gp_pool_plan: plan must be 256-byte aligned");
+  PlanLayout L = plan_layout(m);
+  if (plan_bytes < L.bytes) {
+    gp_set_error("gp_pool_plan: plan buffer %zu < %zu", plan_bytes, L.bytes);
+    return GP_ERR_WORKSPACE;
+  }
+  if (m == 0) return GP_OK;
+  int npow2 = 1;
+  while (npow2 < PT * K) npow2 <<= 1;
+  static bool configured = false;
+  if (!configured) {
+    GP_CUDA(cudaFuncSetAttribute(pool_tc_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    configured = true;
+  }
+  char* p = (char*)plan;
+  pool_tc_plan_kernel<<<(unsigned)L.tiles, 256, npow2 * sizeof(uint32_t), (cudaStream_t)stream>>>(
+      nbr_sorted, weights, m, K, npow2, (int32_t*)(p + L.off_count), (int32_t*)(p + L.off_uidx),
+      (uint8_t*)(p + L.off_w));
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+extern "C" size_t gp_pool_tc_workspace_bytes(int64_t m) {
+  if (m < 0) return 0;
+  return 2 * gp_align_up(sizeof(__nv_bfloat16) * 2 * PD * (size_t)m, 1024);
+}
+
+extern "C" int gp_pool_tc(const float* f0, int64_t stride, int D, const void* plan, const int32_t* nbr_sorted,
+                          const float* weights, int64_t m, int K, int T, float* out, void* workspace,
+                          size_t workspace_bytes, gp_stream_t stream) {
+  GP_CHECK_ARG(m >= 0 && K >= 1 && K <= 128 && T >= 1, "gp_pool_tc: bad sizes (T >= 1)");
+  GP_CHECK_ARG(D == PD, "gp_pool_tc: D must be %d", PD);
+  GP_CHECK_ARG(stride % 4 == 0 && stride >= D && ((uintptr_t)f0 % 16) == 0 && ((uintptr_t)out % 16) == 0,
+               "gp_pool_tc: alignment");
+  GP_CHECK_ARG(((uintptr_t)workspace % 256) == 0 && ((uintptr_t)plan % 256) == 0, "gp_pool_tc: 256-byte alignment");
+  if (workspace_bytes < gp_pool_tc_workspace_bytes(m)) {
+    gp_set_error("gp_pool_tc: workspace %zu < %zu", workspace_bytes, gp_pool_tc_workspace_bytes(m));
+    return GP_ERR_WORKSPACE;
+  }
+  if (m == 0) return GP_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  static int sm_count = 0;
+  if (!sm_count) {
+    int dev = 0;
+    GP_CUDA(cudaGetDevice(&dev));
+    GP_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+    GP_CUDA(cudaFuncSetAttribute(pool_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PSMEM));
+  }
+  PlanLayout L = plan_layout(m);
+  const char* p = (const char*)plan;
+  __nv_bfloat16* planes[2];
+  planes[0] = (__nv_bfloat16*)workspace;
+  planes[1] = (__nv_bfloat16*)((char*)workspace + gp_align_up(sizeof(__nv_bfloat16) * 2 * PD * (size_t)m, 1024));
+  {
+    int64_t tot = m * (PD / 4);
+    pool_tc_split_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(f0, stride, m, planes[0]);
+    GP_LAUNCH_CHECK();
+  }
+  PoolParams P;
+  P.ucount = (const int32_t*)(p + L.off_count);
+  P.uidx = (const int32_t*)(p + L.off_uidx);
+  P.wplan = (const uint8_t*)(p + L.off_w);
+  P.m = m;
+  P.tiles = (int)L.tiles;
+  int grid = P.tiles < sm_count ? P.tiles : sm_count;
+  for (int t = 0; t < T; ++t) {
+    const bool last = t == T - 1;
+    P.fin = planes[t & 1];
+    P.out_planes = last ? nullptr : planes[(t + 1) & 1];
+    P.out_f32 = last ? out : nullptr;
+    pool_tc_kernel<<<grid, PTHREADS, PSMEM, st>>>(P);
+    GP_LAUNCH_CHECK();
+    pool_rows_planes_kernel<<<P.tiles, 256, 0, st>>>(P.fin, P.ucount, nbr_sorted, weights, m, K, P.out_planes,
+                                                     P.out_f32);
+    GP_LAUNCH_CHECK();
+  }
+  return GP_OK;
+}

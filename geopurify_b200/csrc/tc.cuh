@@ -61,6 +61,13 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap
       : "memory");
 }
 
+// 1-D bulk copy global -> shared, completion on an mbarrier (size multiple of 16 bytes, 16-byte aligned)
+__device__ __forceinline__ void bulk_load(uint32_t dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_smem),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05 / TMEM
 template <int COLS>
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem) {  // one full warp
@@ -123,8 +130,14 @@ __device__ __forceinline__ uint32_t swizzled_chunk(int row, int chunk) {
 }
 
 // instruction descriptor, kind::f16: D fp32, A/B bf16, both K-major, shape M x N
-__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, bool b_mn_major = false) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) |
+         ((uint32_t)(M >> 4) << 24);
+}
+// MN-major operand, SWIZZLE_128B: atoms of 64 elements (128 bytes, MN contiguous) x 8 K-rows, 1024 bytes each;
+// lbo = bytes between atoms along MN, sbo = bytes between atoms along K
+__host__ __device__ constexpr uint64_t umma_desc_mnmajor_sw128_base(uint32_t lbo, uint32_t sbo) {
+  return ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 }
 
 }  // namespace tc

@@ -196,12 +196,26 @@ def affinity_softmax(embed, nbr_sorted, sharpen=20.0):
     return w
 
 
-def pool(f0, D, nbr_sorted, weights, T):
-    """T applications of the affinity matrix; returns a [m,D] tensor (or f0 itself when T == 0)."""
+def pool(f0, D, nbr_sorted, weights, T, tensor_core=None):
+    """T applications of the affinity matrix; returns a [m,D] tensor (or f0 itself when T == 0).
+    D == 512 runs on the tensor cores (per-scene plan + tcgen05 block GEMM); other widths one warp per row."""
     lib = L.load()
     m, k = nbr_sorted.shape
     if T == 0:
         return f0
+    if tensor_core is None:
+        tensor_core = D == 512
+    if tensor_core:
+        nbp = lib.gp_pool_plan_bytes(m, k)
+        plan = _ws(nbp)
+        L.check(lib.gp_pool_plan(L.ptr(nbr_sorted), L.ptr(weights), m, k, L.ptr(plan), nbp, L.stream()))
+        nbw = lib.gp_pool_tc_workspace_bytes(m)
+        ws = _ws(nbw)
+        out = torch.empty((m, D), dtype=torch.float32, device=_dev())
+        L.check(lib.gp_pool_tc(L.ptr(f0), f0.stride(0), D, L.ptr(plan), L.ptr(nbr_sorted), L.ptr(weights), m, k, T,
+                               L.ptr(out), L.ptr(ws), nbw, L.stream()))
+        L.count(2 + 2 * T)
+        return out
     a = torch.empty((m, D), dtype=torch.float32, device=_dev())
     b = torch.empty((m, D), dtype=torch.float32, device=_dev()) if T > 1 else a
     outp = ctypes.c_void_p()

@@ -173,6 +173,20 @@ int gp_affinity_softmax(const float* embed, int E, const int32_t* nbr_sorted, in
 int gp_pool(const float* f0, int64_t stride, int D, const int32_t* nbr_sorted, const float* weights, int64_t m,
             int K, int T, float* buf_a, float* buf_b, float** out_host, gp_stream_t stream);
 
+/* ---- A10+A11 on the tensor cores (tcgen05 + TMEM): F <- A F as a block-local dense GEMM.  A per-scene plan groups
+ * 128 consecutive (Morton-sorted) voxels with the sorted union of their neighbour lists and the dense bf16 hi/lo
+ * weight block; every application gathers each union row once per tile and accumulates 128 x 512 fp32 outputs in
+ * TMEM (3 bf16 MMAs per product term).  F moves between applications as bf16 hi/lo planes; the last application
+ * writes float32.  D must be 512, T >= 1; `nbr_sorted` / `weights` serve tiles whose union exceeds 2048 rows.
+ *   out (out) [m, 512] float32;  plan / workspace 256-byte aligned */
+size_t gp_pool_plan_bytes(int64_t m, int K);
+int gp_pool_plan(const int32_t* nbr_sorted, const float* weights, int64_t m, int K, void* plan, size_t plan_bytes,
+                 gp_stream_t stream);
+size_t gp_pool_tc_workspace_bytes(int64_t m);
+int gp_pool_tc(const float* f0, int64_t stride, int D, const void* plan, const int32_t* nbr_sorted,
+               const float* weights, int64_t m, int K, int T, float* out, void* workspace, size_t workspace_bytes,
+               gp_stream_t stream);
+
 /* ---- A11 tail: scene_features[n, 0:D) = pooled[rank[p2v_orig[n]], 0:D) (models/affinity_module.py:1589). */
 int gp_gather_rows(const float* rows, int64_t row_stride, int D, const int32_t* index, int64_t n, float* out,
                    gp_stream_t stream);

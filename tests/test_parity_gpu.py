@@ -248,3 +248,21 @@ def test_student_tensor_core_vs_simt_vs_oracle(scene_run):
     st.precision = "bf16x3"
     print("student max-abs vs oracle:", errs)
     assert errs["fp32"] < 2e-5 and errs["bf16x3"] < 2e-4, errs
+
+
+def test_pool_tensor_core_vs_rowwise(gp):
+    """tcgen05 pooling (D=512) against the fp32 one-warp-per-row kernel: clustered neighbour lists, ragged last tile."""
+    torch.manual_seed(0)
+    m, K, T = 128 * 9 + 37, 24, 3
+    base = torch.arange(m, device="cuda")[:, None] + torch.arange(-40, 41, device="cuda")[None, :]
+    base = base.clamp(0, m - 1)
+    nb = torch.stack([base[i][torch.randperm(81, device="cuda")] for i in range(m)])
+    nb = torch.stack([torch.unique(nb[i])[:K] if torch.unique(nb[i]).numel() >= K else nb[i][:K] for i in range(m)])
+    nb = nb.int().contiguous()
+    w = torch.softmax(2 * torch.randn(m, K, device="cuda"), 1).contiguous()
+    f = torch.nn.functional.normalize(torch.randn(m, 512, device="cuda"), dim=1) * 0.7
+    a = gp.pool(f, 512, nb, w, T, tensor_core=True)
+    b = gp.pool(f, 512, nb, w, T, tensor_core=False)
+    err = (a - b).abs().max().item()
+    print("pool tc vs rowwise max-abs", err)
+    assert err < 2e-5
