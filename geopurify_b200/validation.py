@@ -72,12 +72,42 @@ def mean_iou(inter_sum, union_sum, target_sum):
     return float(np.mean(iou_class)), float(np.mean(acc_class)), float(sum(i) / (sum(t) + 1e-10))
 
 
+def shard_scenes(n_scenes, rank=0, world=1, sizes=None):
+    """Scene indices of `rank` out of `world` processes (one process per GPU).
+    Default: round-robin i = r (mod W).  With `sizes` (points per scene) scenes are dealt longest-first so the
+    ranks finish together.  The reference's own contiguous split is `get_batch_scenes` (run/validation.py:269-280)."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError(f"bad rank/world {rank}/{world}")
+    order = list(range(n_scenes))
+    if sizes is not None:
+        if len(sizes) != n_scenes:
+            raise ValueError("sizes must have one entry per scene")
+        order.sort(key=lambda i: (-int(sizes[i]), i))
+    return order[rank::world]
+
+
+def reduce_histograms(hist, group=None):
+    """The path's one exchange step: sum the [3,C] int64 histogram block over all ranks (NCCL on CUDA tensors,
+    gloo on CPU tensors).  Replaces the dead all_reduce calls at run/validation.py:441-450.  No-op when
+    torch.distributed is not initialised."""
+    import torch.distributed as dist
+    if hist.dtype != torch.int64:
+        raise TypeError("histograms are accumulated in int64 (exact) and reduced as such")
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
+    return hist
+
+
 @torch.no_grad()
-def validate(val_loader, model, test_classes, test_ignore_label, logger=None):
+def validate(val_loader, model, test_classes, test_ignore_label, logger=None, rank=0, world=1):
     """Loop body of run/validation.py:376-553 (All-classes meters).  Returns (mIoU, mAcc, allAcc) and the
-    three float32 running sums."""
+    three float32 running sums.  With world > 1 each rank evaluates the scenes `shard_scenes` gives it and the
+    sums are all-reduced once at the end (exact int64), so every rank returns the same numbers."""
     im, um, tm = AverageMeter(), AverageMeter(), AverageMeter()
+    mine = set(shard_scenes(len(val_loader), rank, world)) if world > 1 else None
     for i, batch_data in enumerate(val_loader):
+        if mine is not None and i not in mine:
+            continue
         if batch_data is None:
             continue
         scene_coords, scene_label = batch_data[0], batch_data[3]
@@ -89,5 +119,12 @@ def validate(val_loader, model, test_classes, test_ignore_label, logger=None):
         tm.update(tgt.cpu().numpy())
         if logger:
             logger.info("Process: [{}/{}]".format(i, len(val_loader)))
-    miou, macc, allacc = mean_iou(im.sum, um.sum, tm.sum)
-    return (miou, macc, allacc), (im.sum, um.sum, tm.sum)
+    c = test_classes
+    sums = [np.asarray(x.sum, dtype=np.float64) if x.count else np.zeros(c) for x in (im, um, tm)]
+    if world > 1:
+        block = torch.as_tensor(np.stack(sums)).round().to(torch.int64)
+        if torch.distributed.get_backend() == "nccl":
+            block = block.cuda()
+        sums = list(reduce_histograms(block).cpu().numpy().astype(np.float32))
+    miou, macc, allacc = mean_iou(sums[0], sums[1], sums[2])
+    return (miou, macc, allacc), (sums[0], sums[1], sums[2])
