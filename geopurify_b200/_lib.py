@@ -39,6 +39,9 @@ _SIGS = {
                                    c_int, c_int, _P, c_int64, _P, _P]),
     "gp_expand_idmap": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P]),
     "gp_lift_mean_pix": (c_int, [_P, c_int64, c_int, c_int, c_int, _P, _P, c_int, c_int, _P, c_int64, _P, _P]),
+    "gp_lift_consensus_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int, c_int]),
+    "gp_lift_consensus": (c_int, [_P, c_int64, c_int, c_int, c_int, _P, _P, _P, c_int, c_int, _P, c_int, c_float, _P,
+                                  c_float, _P, c_int64, _P, _P, c_size_t, _P]),
     "gp_nn1_fill_workspace_bytes": (c_size_t, [c_int64]),
     "gp_nn1_fill": (c_int, [_P, c_int64, _P, c_float, _P, _P, c_size_t, _P]),
     "gp_copy_rows": (c_int, [_P, c_int64, c_int, c_int64, _P, _P]),

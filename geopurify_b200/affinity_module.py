@@ -42,6 +42,8 @@ class SceneInputs:
     cut: int
     vis_thres: float
     labels: Optional[torch.Tensor] = None   # [N] int64
+    idmaps: Optional[torch.Tensor] = None   # [V,H,W] uint8  compact 2-D form (consensus lifting): mask id per pixel
+    tables: Optional[torch.Tensor] = None   # [V,Q,D] float32 mask embeddings, all-zero row = no mask
 
 
 class SonataXAffinityTrainer:
@@ -53,7 +55,7 @@ class SonataXAffinityTrainer:
 
     def __init__(self, cfg=None, text_features=None, logit_scale=100.0, view_features=None, student=None,
                  feature_dim=512, K=None, n_pool=None, sharpen=None, min_visible=400, fill_cell=0.05,
-                 device="cuda"):
+                 device="cuda", mask_features=None, lifting=None):
         L.require_cuda()
         self.cfg = cfg
         self.device = torch.device(device)
@@ -63,7 +65,10 @@ class SonataXAffinityTrainer:
         self.text_features = None if text_features is None else torch.as_tensor(text_features).float().to(self.device)
         self.logit_scale = float(logit_scale)
         self.view_features = view_features
-        self.use_lseg = True
+        self.mask_features = mask_features
+        # "mean" = lift_lseg_features (A4), "consensus" = lift_xdecoder_features (A5, the reference's default teacher)
+        self.lifting = lifting or ("consensus" if (mask_features is not None and view_features is None) else "mean")
+        self.use_lseg = self.lifting == "mean"
         if K is not None:
             self.K = K
         if n_pool is not None:
@@ -114,6 +119,23 @@ class SonataXAffinityTrainer:
         ops.copy_rows(out, d, nn)
         return out, self.text_features, self.logit_scale
 
+    @torch.no_grad()
+    def lift_xdecoder_features(self, batch_data):
+        """Mask-embedding gather, per-view fill, consensus top-3 fusion, scene-level 1-NN fill
+        (models/affinity_module.py:455-714 minus the X-Decoder forward and its mask post-processing).
+        `self.mask_features(batch_data)` supplies (idmap [V,H,W] uint8, table [V,Q,D] float32) on the device: the
+        panoptic-style partition of :544-570 and the kept queries' embeddings."""
+        scene_coords = batch_data[0]
+        idmap, table = self.mask_features(batch_data)
+        w, d = idmap.shape[2], table.shape[2]
+        pix = self.pixels_from_batch(batch_data, w)
+        xyz = scene_coords.float().cuda().contiguous()
+        out, seen = ops.lift_consensus(pix, None, idmap, table, self.text_features, self.logit_scale, xyz,
+                                       self.fill_cell)
+        nn = ops.nn1_fill(xyz, seen, self.fill_cell)
+        ops.copy_rows(out, d, nn)
+        return out, self.text_features, self.logit_scale
+
     # ------------------------------------------------------------------ stages 2-3
     @torch.no_grad()
     def purify(self, lifted, gauss, voxel_coords_i32, p2v_i32, extent, keep_intermediates=False):
@@ -146,7 +168,10 @@ class SonataXAffinityTrainer:
     @torch.no_grad()
     def evaluate_scene(self, batch_data, vis_prefix="scene0695_00", keep_intermediates=False):
         """Reference signature and return value (models/affinity_module.py:1490-1608)."""
-        f_full, text_features, logit_scale = self.lift_lseg_features(batch_data)
+        if self.use_lseg:
+            f_full, text_features, logit_scale = self.lift_lseg_features(batch_data)      # :1498
+        else:
+            f_full, text_features, logit_scale = self.lift_xdecoder_features(batch_data)  # :1500
         scene_coords_3d, inds = batch_data[1], batch_data[2]
         gauss = batch_data[19][:, :6].float().cuda().contiguous()
         vox = scene_coords_3d.to(torch.int32)
@@ -166,10 +191,15 @@ class SonataXAffinityTrainer:
         W, H = s.image_dim
         d = self.feature_dim
         self._mark("begin")
-        _, counts = ops.project_views(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres)
+        pix, counts = ops.project_views(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres)
         keep = ops.accept_views(counts, self.min_visible)
         self._mark("project")
-        lifted, seen = ops.lift_mean_fused(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, keep, s.feat)
+        if self.lifting == "consensus":
+            lifted, seen = ops.lift_consensus(pix, keep, s.idmaps, s.tables, self.text_features, self.logit_scale,
+                                              s.coords_f32, self.fill_cell)
+        else:
+            lifted, seen = ops.lift_mean_fused(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, keep,
+                                               s.feat)
         self._mark("lift")
         nn = ops.nn1_fill(s.coords_f32, seen, self.fill_cell)
         ops.copy_rows(lifted, d, nn)
@@ -211,7 +241,9 @@ def scene_inputs_from_synth(scene, feat_dtype=torch.bfloat16, device="cuda", coo
                        p2v=torch.as_tensor(scene.inds_reconstruct.astype(np.int32)).to(dev), extent=extent, w2c=w2c,
                        intr=intr_d, depth=torch.as_tensor(scene.depth).to(dev).contiguous(), feat=feat,
                        image_dim=(W, H), cut=scene.cut, vis_thres=scene.vis_thres,
-                       labels=torch.as_tensor(scene.labels).to(dev))
+                       labels=torch.as_tensor(scene.labels).to(dev),
+                       idmaps=torch.as_tensor(scene.idmaps).to(dev).contiguous(),
+                       tables=torch.as_tensor(scene.tables).to(dev).float().contiguous())
 
 
 # ---------------------------------------------------------------------- host-buffer entry (the e2e call)
@@ -259,15 +291,16 @@ def host_scene_from_synth(scene, pin=True):
     return HostScene(t=t, extent=extent, image_dim=tuple(scene.image_dim), cut=scene.cut, vis_thres=scene.vis_thres)
 
 
-def upload_scene(h: HostScene, feat_dtype=torch.bfloat16, feat_out=None):
+def upload_scene(h: HostScene, feat_dtype=torch.bfloat16, feat_out=None, dense=True):
     """Host -> device copies of every field (async on the current stream, pinned sources) + the dense feature map
-    built on the device from (idmaps, tables).  Returns SceneInputs."""
+    built on the device from (idmaps, tables) (`dense=False` skips it: consensus lifting reads the compact form).
+    Returns SceneInputs."""
     d = {n: v.cuda(non_blocking=True) for n, v in h.t.items()}
-    feat = ops.expand_idmap(d["idmaps"], d["tables"], feat_dtype, out=feat_out)
+    feat = ops.expand_idmap(d["idmaps"], d["tables"], feat_dtype, out=feat_out) if dense else None
     return SceneInputs(coords=d["coords"], coords_f32=d["coords_f32"], gauss=d["gauss"],
                        voxel_coords=d["voxel_coords"], p2v=d["p2v"], extent=h.extent, w2c=d["w2c"], intr=d["intr"],
                        depth=d["depth"], feat=feat, image_dim=h.image_dim, cut=h.cut, vis_thres=h.vis_thres,
-                       labels=d["labels"])
+                       labels=d["labels"], idmaps=d["idmaps"], tables=d["tables"])
 
 
 def run_scene_host(model, h: HostScene, ignore, feat_dtype=torch.bfloat16, feat_out=None):

@@ -34,7 +34,7 @@ static void nn1_layout(int64_t n, Nn1Layout& L) {
   L.off_vout = take(sizeof(int32_t) * (size_t)n);
   L.cub_bytes = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, L.cub_bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr,
-                                  (const int32_t*)nullptr, (int32_t*)nullptr, (int)n, 0, 22);
+                                  (const int32_t*)nullptr, (int32_t*)nullptr, (int)n, 0, 23);
   L.off_cub = take(L.cub_bytes + 256);
   L.total = off;
 }
@@ -104,8 +104,10 @@ __global__ void nn1_keys_kernel(const float* __restrict__ xyz, const uint8_t* __
   int cx, cy, cz;
   nn1_cell_of(h, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], cx, cy, cz);
   uint32_t key = (uint32_t)((cz * NN1_MAX_DIM + cy) * NN1_MAX_DIM + cx);
-  if (seen[i]) nn[i] = (int32_t)i;
-  else key |= 1u << 21;  // unseen points sort after every seen one, in cell order
+  const uint8_t st = seen[i];
+  if (st == 1) nn[i] = (int32_t)i;
+  else if (st == 0) key |= 1u << 21;  // unseen points sort after every seen one, in cell order
+  else key |= 1u << 22;               // state 2: neither a source nor a query (nn[i] left untouched)
   keys[i] = key;
   vals[i] = (int32_t)i;
 }
@@ -167,7 +169,7 @@ __global__ void __launch_bounds__(256) nn1_query_kernel(const float* __restrict_
   const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (w >= n) return;
   const int64_t spos = n - 1 - w;
-  if ((keys_sorted[spos] >> 21) == 0) return;  // a seen point: every later warp is seen as well
+  if ((keys_sorted[spos] >> 21) != 1) return;  // only unseen points (state 0) are queries
   const int i = vals_sorted[spos];
   const float x = xyz[3 * (int64_t)i], y = xyz[3 * (int64_t)i + 1], z = xyz[3 * (int64_t)i + 2];
   int qx, qy, qz;
@@ -251,7 +253,7 @@ extern "C" int gp_nn1_fill(const float* xyz, int64_t n, const uint8_t* seen, flo
   nn1_keys_kernel<<<grid, 256, 0, st>>>(xyz, seen, n, h, kin, vin, nn);
   GP_LAUNCH_CHECK();
   size_t cb = L.cub_bytes + 256;
-  GP_CUDA(cub::DeviceRadixSort::SortPairs(ws + L.off_cub, cb, kin, kout, vin, vout, (int)n, 0, 22, st));
+  GP_CUDA(cub::DeviceRadixSort::SortPairs(ws + L.off_cub, cb, kin, kout, vin, vout, (int)n, 0, 23, st));
   nn1_cells_kernel<<<grid, 256, 0, st>>>(xyz, kout, vout, n, (float4*)(ws + L.off_sorted), cells);
   nn1_query_kernel<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(xyz, n, h, kout, vout, (const float4*)(ws + L.off_sorted),
                                                            cells, nn);

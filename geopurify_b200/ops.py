@@ -112,6 +112,27 @@ def lift_mean_pix(pix, keep, feat, H, W, out=None, out_stride=None):
     return out, seen
 
 
+def lift_consensus(pix, keep, idmap_u8, table_f32, text, logit_scale, xyz_f32, cell=0.05, out=None, out_stride=None):
+    """A5 lifting from the compact 2-D form (models/affinity_module.py:584-685).  Returns (out [n,stride] f32,
+    seen [n] u8); never-seen rows are zero (fill them with nn1_fill + copy_rows)."""
+    lib = L.load()
+    V, n = pix.shape
+    _, H, W = idmap_u8.shape
+    Q, D = table_f32.shape[1], table_f32.shape[2]
+    C = text.shape[0]
+    if out is None:
+        out_stride = out_stride or D
+        out = torch.empty((n, out_stride), dtype=torch.float32, device=_dev())
+    seen = torch.empty((n,), dtype=torch.uint8, device=_dev())
+    nb = lib.gp_lift_consensus_workspace_bytes(n, V, Q, D, C)
+    ws = _ws(nb)
+    L.check(lib.gp_lift_consensus(L.ptr(pix), n, V, H, W, L.ptr(keep), L.ptr(idmap_u8), L.ptr(table_f32), Q, D,
+                                  L.ptr(text), C, float(logit_scale), L.ptr(xyz_f32), float(cell), L.ptr(out),
+                                  out.stride(0), L.ptr(seen), L.ptr(ws), nb, L.stream()))
+    L.count(4 + 10 * V)
+    return out, seen
+
+
 def nn1_fill(xyz, seen, cell=0.05):
     """Nearest seen point of every unseen point: nn [N] int32 (nn[i]=i when seen)."""
     lib = L.load()

@@ -86,10 +86,29 @@ int gp_expand_idmap(const uint8_t* idmap, const float* table, int V, int H, int 
 int gp_lift_mean_pix(const int32_t* pix, int64_t n, int V, int H, int W, const uint8_t* keep, const void* feat,
                      int feat_dtype, int D, float* out, int64_t out_stride, uint8_t* seen, gp_stream_t stream);
 
+/* ---- A5: X-Decoder-style lifting = mask-embedding gather + per-view hole fill + consensus top-3 fusion
+ * (models/affinity_module.py:584-592, 601-630, 633-685).  The 2-D side is in its compact form:
+ *   pix    [V,n]   int32 from gp_project_views (or the loader's x_label/y_label/mask_2d)
+ *   idmap  [V,H,W] uint8 index of the mask covering each pixel;  table [V,Q,D] float32 mask embeddings, an all-zero
+ *          row meaning "no mask" (the reference's zero feature rows, detected by sum(dim=1) == 0)
+ *   text   [C,D] float32 raw (normalised inside), C <= 256;  xyz [n,3] float32 coordinates for the per-view 1-NN fill
+ *   out (out) [n, out_stride] float32 fused feature in columns [0,D), zeros for never-seen points (fill them with
+ *          gp_nn1_fill + gp_copy_rows, :687-696);  seen (out) [n] uint8
+ * Per view: a visible point under a zero row takes the mask of the nearest visible point under a non-zero row
+ * (a view whose rows are all zero contributes zero features); rows are L2-normalised; logits = scale * f t^T.
+ * Per point: mean logits over its views -> consensus class (lowest index on ties) -> top-min(3, #views) views by
+ * their logit of that class (earliest view on ties) -> softmax weights -> weighted sum. */
+size_t gp_lift_consensus_workspace_bytes(int64_t n, int V, int Q, int D, int C);
+int gp_lift_consensus(const int32_t* pix, int64_t n, int V, int H, int W, const uint8_t* keep, const uint8_t* idmap,
+                      const float* table, int Q, int D, const float* text, int C, float logit_scale,
+                      const float* xyz, float cell, float* out, int64_t out_stride, uint8_t* seen, void* workspace,
+                      size_t workspace_bytes, gp_stream_t stream);
+
 /* ---- hole fill: 1-NN over float xyz (sklearn KDTree k=1 at models/affinity_module.py:445-449, 693-696;
  * run/validation.py:425-430).  For every point with seen==0 finds the nearest seen point (float64 distance on
  * the float32 coordinates, ties -> lowest index) and writes nn[i] = that index; nn[i] = i for seen points,
- * -1 everywhere if no point is seen.  `cell` is the search-grid cell size in coordinate units. */
+ * -1 everywhere if no point is seen.  `cell` is the search-grid cell size in coordinate units.
+ * seen[i] == 2 marks a point that is neither a source nor a query (nn[i] is left untouched). */
 size_t gp_nn1_fill_workspace_bytes(int64_t n);
 int gp_nn1_fill(const float* xyz, int64_t n, const uint8_t* seen, float cell, int32_t* nn, void* workspace,
                 size_t workspace_bytes, gp_stream_t stream);

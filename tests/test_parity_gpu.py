@@ -266,3 +266,57 @@ def test_pool_tensor_core_vs_rowwise(gp):
     err = (a - b).abs().max().item()
     print("pool tc vs rowwise max-abs", err)
     assert err < 2e-5
+
+
+# ----------------------------------------------------------------------------- A5 consensus lifting
+def _consensus_inputs(sc, ref):
+    """Compact 2-D form with mask 0 of every view (and all of view `kept[1]`) turned into "no mask"."""
+    tables = sc.tables.copy()
+    tables[:, 0, :] = 0.0
+    kept = list(ref["kept"])
+    if len(kept) > 2:
+        tables[kept[1]] = 0.0          # a view with no surviving mask contributes zero features
+    pids, vpf = [], []
+    for v in kept:
+        m = ref["mappings"][v]
+        pid = np.nonzero(m[:, 2])[0]
+        pids.append(pid)
+        vpf.append(tables[v][sc.idmaps[v][m[pid, 0], m[pid, 1]]])
+    return tables, pids, vpf
+
+
+def test_lift_consensus_matches_oracle(gp, scene_run):
+    from oracle import oracle
+    sc, model, s, ref = scene_run["sc"], scene_run["model"], scene_run["s"], scene_run["ref"]
+    W, H = sc.image_dim
+    tables, pids, vpf = _consensus_inputs(sc, ref)
+    want, want_seen = oracle.lift_consensus(sc.n_points, sc.coords, vpf, pids, sc.text, sc.logit_scale,
+                                            feat_dim=tables.shape[2])
+    pix, _ = gp.project_views(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres)
+    text = torch.as_tensor(sc.text).float().cuda()
+    got, seen = gp.lift_consensus(pix, model.last_keep, torch.as_tensor(sc.idmaps).cuda(),
+                                  torch.as_tensor(tables).cuda(), text, sc.logit_scale, s.coords_f32)
+    assert (seen.cpu().numpy().astype(bool) == want_seen.numpy()).all()
+    nn = gp.nn1_fill(s.coords_f32, seen)
+    gp.copy_rows(got, tables.shape[2], nn)
+    err = (got.cpu() - want).abs().max(1).values
+    # discrete choices (consensus class, top-3 views, nearest non-zero point) must agree: a wrong choice shows up
+    # as an O(0.1) row error, rounding differences stay below 1e-5
+    assert int((err > 1e-5).sum()) == 0, f"{int((err > 1e-5).sum())} rows differ, max {err.max():.3e}"
+
+
+def test_lift_consensus_single_view_is_normalised_embedding(gp):
+    n, V, H, W, Q, D, C = 64, 1, 4, 4, 3, 128, 5
+    rng = np.random.default_rng(0)
+    table = torch.as_tensor(rng.standard_normal((V, Q, D)).astype(np.float32)).cuda()
+    idmap = torch.as_tensor(rng.integers(0, Q, (V, H, W)).astype(np.uint8)).cuda()
+    pix = torch.as_tensor(rng.integers(0, H * W, (V, n)).astype(np.int32)).cuda()
+    pix[0, ::7] = -1
+    text = torch.as_tensor(rng.standard_normal((C, D)).astype(np.float32)).cuda()
+    xyz = torch.as_tensor(rng.random((n, 3)).astype(np.float32)).cuda()
+    out, seen = gp.lift_consensus(pix, None, idmap, table, text, 100.0, xyz)
+    vis = (pix[0] >= 0)
+    assert (seen.bool() == vis).all()
+    want = torch.nn.functional.normalize(table[0][idmap[0].flatten()[pix[0].clamp(min=0).long()].long()], dim=-1)
+    assert (out[vis] - want[vis]).abs().max().item() < 1e-6
+    assert (out[~vis] == 0).all()
