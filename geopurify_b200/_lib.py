@@ -45,6 +45,8 @@ _SIGS = {
     "gp_nn1_fill_workspace_bytes": (c_size_t, [c_int64]),
     "gp_nn1_fill": (c_int, [_P, c_int64, _P, c_float, _P, _P, c_size_t, _P]),
     "gp_copy_rows": (c_int, [_P, c_int64, c_int, c_int64, _P, _P]),
+    "gp_voxelize_workspace_bytes": (c_size_t, [c_int64]),
+    "gp_voxelize": (c_int, [_P, c_int, c_int64, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
     "gp_voxel_index_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
     "gp_voxel_index_build": (c_int, [_P, c_int64, c_int, c_int, c_int, _P, _P, _P, c_size_t, _P]),
     "gp_kernel_map": (c_int, [_P, c_int64, c_int, c_int, c_int, _P, _P]),

@@ -152,6 +152,28 @@ def copy_rows(rows, D, nn):
     return rows
 
 
+def voxelize(coords, xform):
+    """F1 on the device.  coords [n,3] f32/f64 CUDA, xform [3,4] float64 (host array or CUDA tensor).
+    Returns (vox [m,3] int32, inds [m] int32, inds_reconstruct [n] int32, extent tuple); one host sync for m."""
+    lib = L.load()
+    n = coords.shape[0]
+    xf = torch.as_tensor(xform, dtype=torch.float64).reshape(12).to(_dev()).contiguous()
+    vox = torch.empty((n, 3), dtype=torch.int32, device=_dev())
+    inds = torch.empty((n,), dtype=torch.int32, device=_dev())
+    rec = torch.empty((n,), dtype=torch.int32, device=_dev())
+    meta = torch.zeros((4,), dtype=torch.int64, device=_dev())   # m | extent as int32[3] in the next 12 bytes
+    nb = lib.gp_voxelize_workspace_bytes(n)
+    ws = _ws(nb)
+    ext_ptr = ctypes.c_void_p(meta.data_ptr() + 8)
+    L.check(lib.gp_voxelize(L.ptr(coords), L.dtype_code(coords), n, L.ptr(xf), L.ptr(vox), L.ptr(inds), L.ptr(rec),
+                            L.ptr(meta), ext_ptr, L.ptr(ws), nb, L.stream()))
+    L.count(11)
+    host = meta.cpu()
+    m = int(host[0])
+    ext = host[1:3].view(torch.int32)[:3].tolist()
+    return vox[:m], inds[:m], rec, tuple(int(e) for e in ext)
+
+
 class VoxelIndex:
     """Morton-sorted voxel order + cell lists (device workspace)."""
 

@@ -115,6 +115,18 @@ int gp_nn1_fill(const float* xyz, int64_t n, const uint8_t* seen, float cell, in
 /* rows[i, 0:D) = rows[nn[i], 0:D) for nn[i] != i (out-of-place safe: sources are seen rows, never rewritten). */
 int gp_copy_rows(float* rows, int64_t n, int D, int64_t stride, const int32_t* nn, gp_stream_t stream);
 
+/* ---- F1: Voxelizer.voxelize + sparse_quantize (dataset/voxelizer.py:104-121; dataset/voxelization_utils.py:6-18,
+ * 78-96): c = floor(M [x y z 1]^T) in float64, v = c - min(c), FNV-1-style uint64 key per voxel, np.unique on the
+ * keys: voxels numbered in ascending key order, representative = first point of the voxel.
+ *   coords [n,3] float32/float64;  xform [3,4] float64 row-major (device): diag(1/voxel_size) | 0 for the
+ *   identity-augmentation case (or M_r M_v with augmentation)
+ *   vox (out) [n,3] int32 (first m rows valid), inds (out) [n] int32 (first m valid: representative point),
+ *   inds_reconstruct (out) [n] int32 point -> voxel, m_out (out) device int64, extent (out) device int32[3] */
+size_t gp_voxelize_workspace_bytes(int64_t n);
+int gp_voxelize(const void* coords, int coords_dtype, int64_t n, const double* xform, int32_t* vox, int32_t* inds,
+                int32_t* inds_reconstruct, int64_t* m_out, int32_t* extent, void* workspace, size_t workspace_bytes,
+                gp_stream_t stream);
+
 /* ---- voxel index: Morton-sorted order + cell lists over integer voxel coordinates (replaces the MinkowskiEngine
  * coordinate map of models/affinity_module.py:1541-1545 and the faiss index of :1553-1554).
  *   vox         [m,3] int32 non-negative voxel coordinates, unique rows

@@ -213,6 +213,34 @@ def lift_consensus(n_points, scene_xyz, view_point_feats, pids, text, logit_scal
     return out, seen
 
 
+# ----------------------------------------------------------------------------- F1
+def fnv_hash_vec(arr):
+    """dataset/voxelization_utils.py:6-18: uint64 FNV-1-style key, multiply by the prime then xor, per column."""
+    arr = np.asarray(arr).astype(np.uint64)
+    h = np.full(arr.shape[0], np.uint64(14695981039346656037), dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        for j in range(arr.shape[1]):
+            h = h * np.uint64(1099511628211)
+            h = np.bitwise_xor(h, arr[:, j])
+    return h
+
+
+def voxelize(coords, voxel_size=0.02, rigid_transformation=None):
+    """Voxelizer.voxelize without clipping / random augmentation (dataset/voxelizer.py:104-121) followed by
+    sparse_quantize(return_index=True) (dataset/voxelization_utils.py:78-96).
+    Returns (coords_aug[inds] [M,3] float64, inds [M], inds_reconstruct [N])."""
+    coords = np.asarray(coords)
+    if rigid_transformation is None:
+        rigid_transformation = np.eye(4)
+        np.fill_diagonal(rigid_transformation[:3, :3], 1 / voxel_size)                 # voxelizer.py:61-63
+    homo = np.hstack((coords, np.ones((coords.shape[0], 1), dtype=coords.dtype)))      # :107-109
+    aug = np.floor(homo @ rigid_transformation.T[:, :3])                               # :110
+    aug = np.floor(aug - aug.min(0))                                                   # :112-116
+    key = fnv_hash_vec(np.floor(aug / np.array([1, 1, 1])))                            # voxelization_utils.py:76-81
+    _, inds, inv = np.unique(key, return_index=True, return_inverse=True)              # :93
+    return aug[inds], inds, inv.astype(np.int64)
+
+
 # ----------------------------------------------------------------------------- A6
 def scatter_mean(src, index, m=None):
     """torch_scatter.scatter_mean(src, index, dim=0) (models/affinity_module.py:1524-1535):

@@ -144,3 +144,16 @@ def test_view_acceptance_renumbers():
     assert kept == [0, 2] and list(pids[1]) == list(range(2, 9)) and (rows[0] == 3).all()
     kept, *_ = oracle.accept_views(maps, min_visible=6)
     assert kept == [2]
+
+
+VOXEL_CASES = ["surface_f32", "cloud_f64_negative", "single_point", "duplicates", "on_cell_faces"]
+
+
+@pytest.mark.parametrize("name", VOXEL_CASES)
+def test_oracle_voxelizer_matches_reference_golden(golden_dir, name):
+    """F1: the restatement against outputs of the reference's own Voxelizer (tests/golden/make_golden_voxel.py)."""
+    g = np.load(os.path.join(golden_dir, f"voxel_{name}.npz"))
+    vc, inds, rec = oracle.voxelize(g["coords"], float(g["voxel_size"]))
+    assert (vc == g["voxel_coords"]).all() and (inds == g["inds"]).all() and (rec == g["inds_reconstruct"]).all()
+    assert (vc[rec] == np.floor(np.floor(g["coords"].astype(np.float64) * (1 / float(g["voxel_size"]))) -
+                                np.floor(g["coords"].astype(np.float64) * (1 / float(g["voxel_size"]))).min(0))).all()

@@ -320,3 +320,51 @@ def test_lift_consensus_single_view_is_normalised_embedding(gp):
     want = torch.nn.functional.normalize(table[0][idmap[0].flatten()[pix[0].clamp(min=0).long()].long()], dim=-1)
     assert (out[vis] - want[vis]).abs().max().item() < 1e-6
     assert (out[~vis] == 0).all()
+
+
+# ----------------------------------------------------------------------------- F1 voxeliser
+@pytest.mark.parametrize("name", ["surface_f32", "cloud_f64_negative", "single_point", "duplicates", "on_cell_faces"])
+def test_voxelizer_matches_reference_golden(gp, golden_dir, name):
+    from geopurify_b200.voxelizer import Voxelizer
+    g = np.load(os.path.join(golden_dir, f"voxel_{name}.npz"))
+    n = g["coords"].shape[0]
+    feats = np.arange(n * 3, dtype=np.float64).reshape(n, 3)
+    labels = np.arange(n, dtype=np.int64)
+    c, f, l, rec, inds = Voxelizer(voxel_size=float(g["voxel_size"])).voxelize(g["coords"], feats, labels,
+                                                                              return_ind=True)
+    assert c.dtype == np.float64 and (c == g["voxel_coords"]).all()
+    assert (inds == g["inds"]).all() and (rec == g["inds_reconstruct"]).all()
+    assert (f == feats[g["inds"]]).all() and (l == labels[g["inds"]]).all()
+
+
+def test_voxelizer_full_size_and_rotated_vs_oracle(gp):
+    from oracle import oracle
+    from geopurify_b200.voxelizer import Voxelizer
+    sc = synth.make_scene(n_points=150_000, n_views=1, image_dim=(32, 24), feat_dim=8, n_classes=3, seed=5557)
+    c = torch.as_tensor(sc.coords).cuda()
+    vox, inds, rec, ext = Voxelizer(voxel_size=0.02).voxelize_device(c)
+    vc, oi, orec = oracle.voxelize(sc.coords, 0.02)
+    assert (vox.cpu().numpy() == vc).all() and (inds.cpu().numpy() == oi).all() and (rec.cpu().numpy() == orec).all()
+    assert ext == tuple(int(e) + 1 for e in vc.max(0))
+    # round trip: every point's voxel holds its own cell
+    assert (vox[rec.long()].cpu().numpy() == np.floor(np.floor(sc.coords.astype(np.float64) * 50.0) -
+                                                      np.floor(sc.coords.astype(np.float64) * 50.0).min(0))).all()
+    # the generator's own voxelisation (what the rest of the path was tested on) is the same thing
+    assert (sc.voxel_coords == vc).all() and (sc.inds_reconstruct == orec).all()
+    # rotated + scaled transformation (M_r M_v with augmentation on): same dgemm FMA chain as the projection
+    th = 0.3
+    m = np.eye(4)
+    m[:3, :3] = np.array([[np.cos(th), -np.sin(th), 0], [np.sin(th), np.cos(th), 0], [0, 0, 1]]) * 47.3
+    c64 = torch.as_tensor(sc.coords.astype(np.float64)).cuda()
+    vox, inds, rec, _ = Voxelizer(voxel_size=0.02).voxelize_device(c64, m)
+    vc, oi, orec = oracle.voxelize(sc.coords.astype(np.float64), rigid_transformation=m)
+    assert (vox.cpu().numpy() == vc).all() and (inds.cpu().numpy() == oi).all() and (rec.cpu().numpy() == orec).all()
+
+
+def test_voxelizer_argument_errors(gp):
+    from geopurify_b200 import _lib
+    from geopurify_b200.voxelizer import Voxelizer
+    with pytest.raises(NotImplementedError):
+        Voxelizer(voxel_size=0.02, use_augmentation=True)
+    with pytest.raises(_lib.GeoPurifyError):
+        gp.voxelize(torch.zeros((0, 3), device="cuda"), np.eye(4)[:3])
