@@ -7,9 +7,12 @@
 //      (flags -> exclusive scan -> fill); 128-pair tiles never straddle an offset.
 //   2. gather-GEMM (this file's main kernel): C[p, :] = in[pair_in[p], :] W_o for every pair p, one 128 x N tile per
 //      CTA iteration.  A rows are gathered with cp.async (zero-filled tails) from activations stored as bf16 hi/lo
-//      planes, W_o^T tiles arrive by TMA, both in the 32-byte-swizzled K-major layout UMMA reads.  Each K=16 step
-//      issues  Ahi*Bhi + Ahi*Blo + Alo*Bhi  into a 128 x N fp32 accumulator in TMEM; the epilogue warps drain TMEM
-//      to a pair-major staging buffer with coalesced 128-byte row stores.
+//      planes, in K=64 chunks laid out as 128-byte-swizzled K-major rows: 8 consecutive lanes fetch one 128-byte
+//      line of one row, so a warp-wide cp.async touches 4 cache lines (the first version fetched 16 bytes from 32
+//      different rows per instruction and was bound by the L1TEX tag stage at 85 %).  W_o^T slices arrive by TMA in
+//      K=16 stages (32-byte swizzle) from a pre-tiled weight image in which every stage's box is contiguous.  Each
+//      K=16 step issues  Alo*Bhi + Ahi*Blo + Ahi*Bhi  into a 128 x N fp32 accumulator in TMEM; the epilogue warps
+//      drain TMEM to a pair-major staging buffer with coalesced 128-byte row stores.
 //   3. reduce (student_reduce_kernel): out[i] = sum of its staged pair rows in ascending offset order (the oracle's
 //      order, deterministic, no atomics), BN scale/shift, residual, ReLU, then the bf16 hi/lo split for the next layer.
 #include <cub/device/device_scan.cuh>
@@ -21,8 +24,11 @@ namespace {
 constexpr int TM = 128;        // pairs (rows) per tile = UMMA M
 constexpr int BK = 16;         // K per stage = UMMA K for bf16; 32-byte operand rows, SWIZZLE_32B
 constexpr int ROWB = BK * 2;   // bytes per operand row per stage
-constexpr int NSTAGE = 5;
-constexpr int LAG = 3;         // cp.async groups in flight per producer thread
+constexpr int NSTAGE = 3;      // B (weight) stages of K=16
+constexpr int AK = 64;         // K per A chunk: 128-byte operand rows, SWIZZLE_128B
+constexpr int AKS = AK / BK;   // K=16 steps per A chunk
+constexpr int NA = 3;          // A chunk buffers
+constexpr int ALAG = 1;        // A chunks in flight per gather thread besides the one being issued
 constexpr int EPI_LD = 36;     // floats per staged row in the epilogue transpose buffer (16-byte aligned, conflict-free)
 constexpr int NTHREADS = 384;  // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue, 8-11 A gather
 
@@ -35,11 +41,15 @@ struct TileInfo {  // one 128-pair tile
 
 template <int N>
 struct Smem {
-  static constexpr int A_BYTES = TM * ROWB;         // per plane
+  static constexpr int A_BYTES = TM * AK * 2;       // per plane per chunk (16 KB)
+  static constexpr int A_CHUNK = 2 * A_BYTES;       // hi + lo
   static constexpr int B_BYTES = N * ROWB;          // per plane
-  static constexpr int STAGE = 2 * A_BYTES + 2 * B_BYTES;
+  static constexpr int STAGE = 2 * B_BYTES;
+  static constexpr int A_OFF = 0;
+  static constexpr int B_OFF = NA * A_CHUNK;
+  static constexpr int EPI_OFF = B_OFF + NSTAGE * STAGE;
   static constexpr int EPI = 4 * 32 * EPI_LD * 4;
-  static constexpr int BAR_OFF = NSTAGE * STAGE + EPI;
+  static constexpr int BAR_OFF = EPI_OFF + EPI;
   static constexpr int TOTAL = BAR_OFF + 256 + 1024;  // barriers + slack for the 1024-byte alignment of the base
 };
 
@@ -52,7 +62,7 @@ struct GemmParams {
   const int32_t* ntiles_dev;  // number of tiles (device), or nullptr -> ntiles_host
   int ntiles_host;
   int64_t m_rows;          // identity mode: number of rows
-  int cout_total;          // rows per (offset, plane) block of the packed weights (= layer cout)
+  int cout_total;          // rows per (offset, plane, k-step) block of the pre-tiled weights (= layer cout)
   float* c;                // [c_rows][ldc]
   int64_t ldc;
 };
@@ -63,23 +73,30 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
   extern __shared__ uint8_t smem_raw[];
   using S = Smem<N>;
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  float* epi = (float*)(smem + NSTAGE * S::STAGE);
+  float* epi = (float*)(smem + S::EPI_OFF);
   uint64_t* bars = (uint64_t*)(smem + S::BAR_OFF);
-  uint64_t* full = bars;                   // [NSTAGE] A gathered + B landed
-  uint64_t* empty = bars + NSTAGE;         // [NSTAGE] MMAs reading the stage have completed
-  uint64_t* tmem_full = bars + 2 * NSTAGE;  // accumulator complete
-  uint64_t* tmem_empty = tmem_full + 1;     // accumulator drained
+  uint64_t* b_full = bars;                   // [NSTAGE] weight slice landed (TMA)
+  uint64_t* b_empty = b_full + NSTAGE;       // [NSTAGE] MMAs reading the stage have completed
+  uint64_t* a_full = b_empty + NSTAGE;       // [NA] A chunk gathered (4 gather warps)
+  uint64_t* a_empty = a_full + NA;           // [NA] MMAs reading the chunk have completed
+  uint64_t* tmem_full = a_empty + NA;        // accumulator complete
+  uint64_t* tmem_empty = tmem_full + 1;      // accumulator drained
   uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ntiles = P.ntiles_dev ? *P.ntiles_dev : P.ntiles_host;
   const int ksteps = P.kp / BK;
+  const int nchunks = (ksteps + AKS - 1) / AKS;
 
   if (threadIdx.x == 0) {
     tc::tma_prefetch_desc(&wmap);
     for (int s = 0; s < NSTAGE; ++s) {
-      tc::mbar_init(&full[s], 4 + 1);  // 4 gather warps + the TMA thread's expect_tx arrive
-      tc::mbar_init(&empty[s], 1);
+      tc::mbar_init(&b_full[s], 1);
+      tc::mbar_init(&b_empty[s], 1);
+    }
+    for (int s = 0; s < NA; ++s) {
+      tc::mbar_init(&a_full[s], 4);
+      tc::mbar_init(&a_empty[s], 1);
     }
     tc::mbar_init(tmem_full, 1);
     tc::mbar_init(tmem_empty, 4);
@@ -112,50 +129,57 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
         for (int ks = 0; ks < ksteps; ++ks, ++it) {
           const int s = it % NSTAGE;
           const uint32_t ph = (it / NSTAGE) & 1;
-          tc::mbar_wait(&empty[s], ph ^ 1);
-          tc::mbar_arrive_expect_tx(&full[s], 2 * S::B_BYTES);
-          uint8_t* st = smem + s * S::STAGE + 2 * S::A_BYTES;
+          tc::mbar_wait(&b_empty[s], ph ^ 1);
+          tc::mbar_arrive_expect_tx(&b_full[s], 2 * S::B_BYTES);
+          uint8_t* st = smem + S::B_OFF + s * S::STAGE;
 #pragma unroll
           for (int plane = 0; plane < 2; ++plane)
 #pragma unroll
             for (int nb = 0; nb < N / BOX; ++nb)
-              tc::tma_load_2d(tc::smem_u32(st + plane * S::B_BYTES + nb * BOX * ROWB), &wmap, ks * BK,
-                              (ti.offset * 2 + plane) * P.cout_total + nb * BOX, &full[s]);
+              tc::tma_load_2d(tc::smem_u32(st + plane * S::B_BYTES + nb * BOX * ROWB), &wmap, 0,
+                              ((ti.offset * 2 + plane) * ksteps + ks) * P.cout_total + nb * BOX, &b_full[s]);
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint64_t DBASE = tc::umma_desc_kmajor_base<ROWB>();
+    constexpr uint64_t DB = tc::umma_desc_kmajor_base<ROWB>();
+    constexpr uint64_t DA = tc::umma_desc_kmajor_base<AK * 2>();
     constexpr int UN = N < 256 ? N : 256;
     constexpr uint32_t IDESC = tc::umma_idesc_bf16(TM, UN);
-    uint32_t it = 0, tcount = 0;
+    uint32_t it = 0, ac = 0, tcount = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
       tc::mbar_wait(tmem_empty, (tcount & 1) ^ 1);
       tc::tc_fence_after();
       for (int ks = 0; ks < ksteps; ++ks, ++it) {
         const int s = it % NSTAGE;
         const uint32_t ph = (it / NSTAGE) & 1;
-        tc::mbar_wait(&full[s], ph);
+        const int ab = ac % NA;
+        if ((ks & (AKS - 1)) == 0) tc::mbar_wait(&a_full[ab], (ac / NA) & 1);
+        tc::mbar_wait(&b_full[s], ph);
         tc::tc_fence_after();
+        const bool chunk_end = (ks & (AKS - 1)) == AKS - 1 || ks == ksteps - 1;
         if (lane == 0) {
-          const uint32_t a_hi = tc::smem_u32(smem + s * S::STAGE);
+          // K=16 slice j of a 128-byte swizzled row starts 32 j bytes into the (1024-byte aligned) tile
+          const uint32_t a_hi = tc::smem_u32(smem + S::A_OFF + ab * S::A_CHUNK) + (ks & (AKS - 1)) * ROWB;
           const uint32_t a_lo = a_hi + S::A_BYTES;
-          const uint32_t b_hi = a_hi + 2 * S::A_BYTES;
+          const uint32_t b_hi = tc::smem_u32(smem + S::B_OFF + s * S::STAGE);
           const uint32_t b_lo = b_hi + S::B_BYTES;
 #pragma unroll
           for (int h = 0; h < N / UN; ++h) {
             const uint32_t d = tmem_base + h * UN;
             const uint32_t boff = h * UN * ROWB;
             // small terms first, then the leading product
-            tc::umma_bf16(d, tc::umma_desc(DBASE, a_lo), tc::umma_desc(DBASE, b_hi + boff), IDESC, ks > 0);
-            tc::umma_bf16(d, tc::umma_desc(DBASE, a_hi), tc::umma_desc(DBASE, b_lo + boff), IDESC, 1);
-            tc::umma_bf16(d, tc::umma_desc(DBASE, a_hi), tc::umma_desc(DBASE, b_hi + boff), IDESC, 1);
+            tc::umma_bf16(d, tc::umma_desc(DA, a_lo), tc::umma_desc(DB, b_hi + boff), IDESC, ks > 0);
+            tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_lo + boff), IDESC, 1);
+            tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_hi + boff), IDESC, 1);
           }
-          tc::umma_commit(&empty[s]);
+          tc::umma_commit(&b_empty[s]);
+          if (chunk_end) tc::umma_commit(&a_empty[ab]);
           if (ks == ksteps - 1) tc::umma_commit(tmem_full);
         }
         __syncwarp();
+        if (chunk_end) ++ac;
       }
     }
   } else if (warp >= 4 && warp < 8) {
@@ -196,32 +220,37 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
       }
     }
   } else if (warp >= 8) {
-    // ===================== A gather: thread r owns tile row r =====================
-    const int r = threadIdx.x - 256;
-    const uint32_t swz = (r >> 2) & 1;  // SWIZZLE_32B: 16-byte chunk c of row r is stored at chunk c ^ ((r >> 2) & 1)
-    uint32_t it = 0, signalled = 0;
+    // ===================== A gather: warp w owns tile rows [32 w, 32 w + 32); 8 lanes fetch one 128-byte row slice ====
+    const int w = warp - 8;
+    const int rsub = lane >> 3, c = lane & 7;
+    uint32_t ac = 0, signalled = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
       const TileInfo ti = tile_of(t);
-      int in_row = -1;
-      if (r < ti.nrows) in_row = P.pair_in ? __ldg(P.pair_in + ti.p0 + r) : ti.p0 + r;
-      const __nv_bfloat16* src = P.a + (int64_t)(in_row < 0 ? 0 : in_row) * P.lda;
-      const uint32_t nbytes = in_row < 0 ? 0u : 16u;
-      for (int ks = 0; ks < ksteps; ++ks, ++it) {
-        const int s = it % NSTAGE;
-        const uint32_t ph = (it / NSTAGE) & 1;
-        tc::mbar_wait(&empty[s], ph ^ 1);
-        const uint32_t dst = tc::smem_u32(smem + s * S::STAGE) + r * ROWB;
-        const __nv_bfloat16* g = src + ks * BK;
-        tc::cp_async16(dst + ((0 ^ swz) << 4), g, nbytes);
-        tc::cp_async16(dst + ((1 ^ swz) << 4), g + 8, nbytes);
-        tc::cp_async16(dst + S::A_BYTES + ((0 ^ swz) << 4), g + P.kp, nbytes);
-        tc::cp_async16(dst + S::A_BYTES + ((1 ^ swz) << 4), g + P.kp + 8, nbytes);
+      const int r = w * 32 + lane;
+      int my_row = -1;
+      if (r < ti.nrows) my_row = P.pair_in ? __ldg(P.pair_in + ti.p0 + r) : ti.p0 + r;
+      for (int ci = 0; ci < nchunks; ++ci, ++ac) {
+        const int ab = ac % NA;
+        tc::mbar_wait(&a_empty[ab], ((ac / NA) & 1) ^ 1);
+        const int kvalid = min(AK, P.kp - ci * AK);  // elements of this chunk that exist
+        const uint32_t abase = tc::smem_u32(smem + S::A_OFF + ab * S::A_CHUNK);
+#pragma unroll
+        for (int itr = 0; itr < 8; ++itr) {
+          const int rl = itr * 4 + rsub;             // row inside this warp's 32
+          const int in_row = __shfl_sync(0xffffffffu, my_row, rl);
+          const int row = w * 32 + rl;
+          const uint32_t nbytes = (in_row >= 0 && c * 8 < kvalid) ? 16u : 0u;
+          const __nv_bfloat16* g = P.a + (int64_t)(in_row < 0 ? 0 : in_row) * P.lda + ci * AK + (nbytes ? c * 8 : 0);
+          const uint32_t dst = abase + row * (AK * 2) + ((c ^ (row & 7)) << 4);
+          tc::cp_async16(dst, g, nbytes);
+          tc::cp_async16(dst + S::A_BYTES, g + P.kp, nbytes);
+        }
         tc::cp_async_commit();
-        if (it >= LAG) {  // the group issued LAG iterations ago has landed
-          tc::cp_async_wait<LAG>();
+        if (ac >= ALAG) {  // the chunk issued ALAG iterations ago has landed
+          tc::cp_async_wait<ALAG>();
           tc::fence_proxy_async();
           __syncwarp();
-          if (lane == 0) tc::mbar_arrive(&full[signalled % NSTAGE]);
+          if (lane == 0) tc::mbar_arrive(&a_full[signalled % NA]);
           ++signalled;
         }
       }
@@ -229,8 +258,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
     tc::cp_async_wait<0>();
     tc::fence_proxy_async();
     __syncwarp();
-    for (; signalled < it; ++signalled)
-      if (lane == 0) tc::mbar_arrive(&full[signalled % NSTAGE]);
+    for (; signalled < ac; ++signalled)
+      if (lane == 0) tc::mbar_arrive(&a_full[signalled % NA]);
   }
 
   tc::tc_fence_before();
@@ -326,7 +355,8 @@ __global__ void tc_split_input_kernel(const float* __restrict__ x, int64_t strid
   out[r * 2 * kp + kp + c] = lo;
 }
 
-// weights [kv][cin_pad][cout] fp32 -> Wt [kv][2][cout][kp] bf16 (K-major rows, hi plane then lo plane)
+// weights [kv][cin_pad][cout] fp32 -> Wt [kv][2][kp/16][cout][16] bf16: hi plane then lo plane, and inside a plane one
+// contiguous [cout][16] block per K=16 step, so that the TMA box of a stage is one contiguous run of 32-byte rows
 __global__ void tc_pack_weights_kernel(const float* __restrict__ w, int kv, int cin_pad, int cout, int kp,
                                        __nv_bfloat16* __restrict__ out) {
   int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -338,8 +368,9 @@ __global__ void tc_pack_weights_kernel(const float* __restrict__ w, int kv, int 
   float v = k < cin_pad ? w[((int64_t)o * cin_pad + k) * cout + n] : 0.f;
   __nv_bfloat16 hi, lo;
   split_bf16(v, hi, lo);
-  out[(((int64_t)o * 2 + 0) * cout + n) * kp + k] = hi;
-  out[(((int64_t)o * 2 + 1) * cout + n) * kp + k] = lo;
+  const int ks = k / BK, kk = k % BK, nks = kp / BK;
+  out[((((int64_t)o * 2 + 0) * nks + ks) * cout + n) * BK + kk] = hi;
+  out[((((int64_t)o * 2 + 1) * nks + ks) * cout + n) * BK + kk] = lo;
 }
 
 // ------------------------------------------------------------------ reduce: pair rows -> output rows + epilogue
@@ -443,12 +474,13 @@ static EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-// 2-D bf16 tensor [rows][kp] (kp contiguous), box 16 x box_rows, 32-byte swizzle
-static bool make_weight_map(CUtensorMap* map, const void* base, int64_t rows, int kp, int box_rows) {
+// 2-D bf16 tensor [rows][16] (the pre-tiled weight image: row = ((offset*2 + plane) * ksteps + kstep) * cout + n),
+// box 16 x box_rows, 32-byte swizzle
+static bool make_weight_map(CUtensorMap* map, const void* base, int64_t rows, int box_rows) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return false;
-  cuuint64_t dims[2] = {(cuuint64_t)kp, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)kp * 2};
+  cuuint64_t dims[2] = {(cuuint64_t)BK, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)BK * 2};
   cuuint32_t box[2] = {BK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   return fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
@@ -608,7 +640,7 @@ extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weig
   for (int l = 0; l + 1 < d->n_layers; ++l) {
     CUtensorMap map;
     const __nv_bfloat16* wl = (const __nv_bfloat16*)packed + woff;
-    GP_CHECK_ARG(make_weight_map(&map, wl, (int64_t)27 * 2 * H, in_kp, H < 256 ? H : 256),
+    GP_CHECK_ARG(make_weight_map(&map, wl, (int64_t)27 * 2 * H * (in_kp / BK), H < 256 ? H : 256),
                  "gp_student_forward_tc: cuTensorMapEncodeTiled failed (layer %d)", l);
     bool is_res_src = false;
     for (int j = l + 1; j < d->n_layers; ++j) is_res_src |= d->residual_from[j] == l;
@@ -656,7 +688,7 @@ extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weig
   {  // 1^3 output layer: plain GEMM [m, H] x [H, E] straight into `embed`
     const int l = d->n_layers - 1;
     CUtensorMap map;
-    GP_CHECK_ARG(make_weight_map(&map, (const __nv_bfloat16*)packed + woff, 2 * E, H, E),
+    GP_CHECK_ARG(make_weight_map(&map, (const __nv_bfloat16*)packed + woff, (int64_t)2 * E * (H / BK), E),
                  "gp_student_forward_tc: cuTensorMapEncodeTiled failed (output layer)");
     GP_CHECK_ARG(!d->bn[l] && !d->relu[l] && d->residual_from[l] < 0, "gp_student_forward_tc: output layer is linear");
     GemmParams P;
