@@ -12,7 +12,7 @@ from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int64, c_size_
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgeopurify_b200.so")
+LIB_PATH = os.environ.get("GEOPURIFY_B200_LIB") or os.path.join(_HERE, "libgeopurify_b200.so")  # env: A/B builds
 
 GP_F32, GP_F64, GP_BF16 = 1, 2, 3
 

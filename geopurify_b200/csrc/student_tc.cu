@@ -24,10 +24,15 @@ namespace {
 constexpr int TM = 128;        // pairs (rows) per tile = UMMA M
 constexpr int BK = 16;         // K per stage = UMMA K for bf16; 32-byte operand rows, SWIZZLE_32B
 constexpr int ROWB = BK * 2;   // bytes per operand row per stage
-constexpr int NSTAGE = 3;      // B (weight) stages of K=16
-constexpr int AK = 64;         // K per A chunk: 128-byte operand rows, SWIZZLE_128B
+#ifndef GP_STU_NSTAGE
+#define GP_STU_NSTAGE 5
+#define GP_STU_AK 32
+#define GP_STU_NA 3
+#endif
+constexpr int NSTAGE = GP_STU_NSTAGE;  // B (weight) stages of K=16
+constexpr int AK = GP_STU_AK;  // K per A chunk: 64- or 128-byte operand rows, SWIZZLE_64B / SWIZZLE_128B
 constexpr int AKS = AK / BK;   // K=16 steps per A chunk
-constexpr int NA = 3;          // A chunk buffers
+constexpr int NA = GP_STU_NA;  // A chunk buffers
 constexpr int ALAG = 1;        // A chunks in flight per gather thread besides the one being issued
 constexpr int EPI_LD = 36;     // floats per staged row in the epilogue transpose buffer (16-byte aligned, conflict-free)
 constexpr int NTHREADS = 384;  // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue, 8-11 A gather
@@ -50,7 +55,7 @@ struct Smem {
   static constexpr int EPI_OFF = B_OFF + NSTAGE * STAGE;
   static constexpr int EPI = 4 * 32 * EPI_LD * 4;
   static constexpr int BAR_OFF = EPI_OFF + EPI;
-  static constexpr int TOTAL = BAR_OFF + 256 + 1024;  // barriers + slack for the 1024-byte alignment of the base
+  static constexpr int TOTAL = BAR_OFF + 256;         // + barriers
 };
 
 struct GemmParams {
@@ -72,7 +77,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
                                                                       const GemmParams P) {
   extern __shared__ uint8_t smem_raw[];
   using S = Smem<N>;
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_raw;  // dynamic shared memory starts 1024-byte aligned (no static smem in this kernel); checked below
   float* epi = (float*)(smem + S::EPI_OFF);
   uint64_t* bars = (uint64_t*)(smem + S::BAR_OFF);
   uint64_t* b_full = bars;                   // [NSTAGE] weight slice landed (TMA)
@@ -89,6 +94,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
   const int nchunks = (ksteps + AKS - 1) / AKS;
 
   if (threadIdx.x == 0) {
+    if (tc::smem_u32(smem) & 1023u) __trap();
     tc::tma_prefetch_desc(&wmap);
     for (int s = 0; s < NSTAGE; ++s) {
       tc::mbar_init(&b_full[s], 1);
@@ -222,7 +228,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
   } else if (warp >= 8) {
     // ===================== A gather: warp w owns tile rows [32 w, 32 w + 32); 8 lanes fetch one 128-byte row slice ====
     const int w = warp - 8;
-    const int rsub = lane >> 3, c = lane & 7;
+    constexpr int LPR = AK * 2 / 16;   // lanes per row slice (16-byte chunks in AK bf16)
+    constexpr int RPI = 32 / LPR;      // rows per warp-wide cp.async
+    const int rsub = lane / LPR, c = lane % LPR;
     uint32_t ac = 0, signalled = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
       const TileInfo ti = tile_of(t);
@@ -235,13 +243,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
         const int kvalid = min(AK, P.kp - ci * AK);  // elements of this chunk that exist
         const uint32_t abase = tc::smem_u32(smem + S::A_OFF + ab * S::A_CHUNK);
 #pragma unroll
-        for (int itr = 0; itr < 8; ++itr) {
-          const int rl = itr * 4 + rsub;             // row inside this warp's 32
+        for (int itr = 0; itr < 32 / RPI; ++itr) {
+          const int rl = itr * RPI + rsub;           // row inside this warp's 32
           const int in_row = __shfl_sync(0xffffffffu, my_row, rl);
           const int row = w * 32 + rl;
           const uint32_t nbytes = (in_row >= 0 && c * 8 < kvalid) ? 16u : 0u;
           const __nv_bfloat16* g = P.a + (int64_t)(in_row < 0 ? 0 : in_row) * P.lda + ci * AK + (nbytes ? c * 8 : 0);
-          const uint32_t dst = abase + row * (AK * 2) + ((c ^ (row & 7)) << 4);
+          const uint32_t dst = abase + row * (AK * 2) + (tc::swizzled_chunk<AK * 2>(row, c) << 4);
           tc::cp_async16(dst, g, nbytes);
           tc::cp_async16(dst + S::A_BYTES, g + P.kp, nbytes);
         }
