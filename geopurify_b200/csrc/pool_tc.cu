@@ -289,26 +289,35 @@ __global__ void __launch_bounds__(PTHREADS, 1) pool_tc_kernel(const PoolParams P
     }
   } else if (warp >= 8) {
     // ===================== gather of the union rows into the MN-major operand layout =====================
-    // thread r: union row k = r >> 3 of the K-step, 64-column block nb = r & 7 (128 contiguous bytes per plane)
-    const int r = threadIdx.x - 256;
-    const int k = r >> 3, nb = r & 7;
-    // atom (nb, k >> 3) at ((nb * 2 + (k >> 3)) * 1024), row (k & 7) of 128 bytes, 16-byte chunk c at c ^ (k & 7)
-    const uint32_t dst_off = A_STEP + (nb * 2 + (k >> 3)) * 1024 + (k & 7) * 128;
-    const uint32_t sw = k & 7;
+    // warp w owns union rows k = 4w .. 4w+3 of the K-step.  One warp-wide cp.async moves 512 contiguous bytes of one
+    // row plane (4 cache lines); the first version fetched 16 bytes from 32 different lines per instruction.
+    // 16-byte chunk q (0..63) of a row = column block nb = q >> 3, chunk c = q & 7 inside the 128-byte atom row:
+    // atom (nb, k >> 3) at ((nb * 2 + (k >> 3)) * 1024), row (k & 7) of 128 bytes, chunk c stored at c ^ (k & 7).
+    const int w = warp - 8;
     uint32_t it = 0, signalled = 0;
     for (int t = blockIdx.x; t < P.tiles; t += gridDim.x) {
       const int ks_n = ksteps_of(t);
-      const int32_t* ui = P.uidx + (int64_t)t * (KSTEP_CAP * PK);
+      const int32_t* ui = P.uidx + (int64_t)t * (KSTEP_CAP * PK) + 4 * w + (lane & 3);
+      int u_next = ks_n > 0 ? __ldg(ui) : 0;
       for (int ks = 0; ks < ks_n; ++ks, ++it) {
         const int s = it % PNSTAGE;
-        const int u = __ldg(ui + ks * PK + k);
+        const int u_cur = u_next;
+        if (ks + 1 < ks_n) u_next = __ldg(ui + (ks + 1) * PK);  // the next K-step's row ids, one iteration ahead
         tc::mbar_wait(&empty[s], ((it / PNSTAGE) & 1) ^ 1);
-        const __nv_bfloat16* src = P.fin + (int64_t)u * 2 * PD + nb * 64;
-        const uint32_t dst = tc::smem_u32(smem + s * PSTAGE) + dst_off;
+        const uint32_t stage = tc::smem_u32(smem + s * PSTAGE) + A_STEP;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          tc::cp_async16(dst + ((c ^ sw) << 4), src + c * 8, 16);
-          tc::cp_async16(dst + B_PLANE + ((c ^ sw) << 4), src + PD + c * 8, 16);
+        for (int kk = 0; kk < 4; ++kk) {
+          const int k = 4 * w + kk;
+          const int u = __shfl_sync(0xffffffffu, u_cur, kk);
+          const __nv_bfloat16* src = P.fin + (int64_t)u * 2 * PD;
+          const uint32_t rowoff = (k >> 3) * 1024 + (k & 7) * 128;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int q = h * 32 + lane;
+            const uint32_t dst = stage + (q >> 3) * 2048 + rowoff + ((((q & 7) ^ (k & 7))) << 4);
+            tc::cp_async16(dst, src + q * 8, 16);
+            tc::cp_async16(dst + B_PLANE, src + PD + q * 8, 16);
+          }
         }
         tc::cp_async_commit();
         if (it >= PLAG) {
