@@ -5,6 +5,17 @@
 #include "common.cuh"
 
 #define NN1_MAX_DIM 128
+#define NN1_COARSE 8                                  // fine cells per coarse cell and axis
+#define NN1_CDIM (NN1_MAX_DIM / NN1_COARSE)           // coarse cells per axis
+#define NN1_NCELLS (NN1_MAX_DIM * NN1_MAX_DIM * NN1_MAX_DIM)
+#define NN1_NCOARSE (NN1_CDIM * NN1_CDIM * NN1_CDIM)
+
+// cell key, coarse-major: all points of one coarse cell (8^3 fine cells) are contiguous after the sort
+__host__ __device__ __forceinline__ uint32_t nn1_key(int cx, int cy, int cz) {
+  const uint32_t coarse = (uint32_t)(((cz >> 3) * NN1_CDIM + (cy >> 3)) * NN1_CDIM + (cx >> 3));
+  const uint32_t fine = (uint32_t)((((cz & 7) << 3) | (cy & 7)) << 3 | (cx & 7));
+  return (coarse << 9) | fine;
+}
 
 struct Nn1Header {
   float mn[3];
@@ -26,7 +37,7 @@ static void nn1_layout(int64_t n, Nn1Layout& L) {
     return o;
   };
   L.off_hdr = take(sizeof(Nn1Header));
-  L.off_cells = take(sizeof(int2) * (size_t)NN1_MAX_DIM * NN1_MAX_DIM * NN1_MAX_DIM);
+  L.off_cells = take(sizeof(int2) * ((size_t)NN1_NCELLS + NN1_NCOARSE));  // fine table, then the coarse table
   L.off_sorted = take(sizeof(float4) * (size_t)n);
   L.off_kin = take(sizeof(uint32_t) * (size_t)n);
   L.off_kout = take(sizeof(uint32_t) * (size_t)n);
@@ -103,7 +114,7 @@ __global__ void nn1_keys_kernel(const float* __restrict__ xyz, const uint8_t* __
   if (i >= n) return;
   int cx, cy, cz;
   nn1_cell_of(h, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], cx, cy, cz);
-  uint32_t key = (uint32_t)((cz * NN1_MAX_DIM + cy) * NN1_MAX_DIM + cx);
+  uint32_t key = nn1_key(cx, cy, cz);
   const uint8_t st = seen[i];
   if (st == 1) nn[i] = (int32_t)i;
   else if (st == 0) key |= 1u << 21;  // unseen points sort after every seen one, in cell order
@@ -123,6 +134,9 @@ __global__ void nn1_cells_kernel(const float* __restrict__ xyz, const uint32_t* 
   sorted[s] = make_float4(xyz[3 * (int64_t)i], xyz[3 * (int64_t)i + 1], xyz[3 * (int64_t)i + 2], __int_as_float(i));
   if (s == 0 || keys_sorted[s - 1] != k) cells[k].x = (int)s;
   if (s == n - 1 || keys_sorted[s + 1] != k) cells[k].y = (int)s + 1;
+  int2* coarse = cells + NN1_NCELLS;
+  if (s == 0 || (keys_sorted[s - 1] >> 9) != (k >> 9)) coarse[k >> 9].x = (int)s;
+  if (s == n - 1 || (keys_sorted[s + 1] >> 9) != (k >> 9)) coarse[k >> 9].y = (int)s + 1;
 }
 
 // One warp per unseen point.  Unseen points carry sort keys (1 << 21 | own cell), so they sit at the tail of the
@@ -184,7 +198,10 @@ __global__ void __launch_bounds__(256) nn1_query_kernel(const float* __restrict_
   slack = fmax(0.0, fmin(slack, 1.0) - 1e-3) * cell;  // margin for float rounding of the cell assignment
   double best = 1e300;
   int besti = 0x7fffffff;
-  for (int r = 0; r <= rmax; ++r) {
+  bool done = false;
+  // ---- phase 1: fine shells around the query's own cell (holes inside seen regions resolve here)
+  const int r1 = min(rmax, 2);
+  for (int r = 0; r <= r1 && !done; ++r) {
     const int wd = 2 * r + 1;
     const int total = r == 0 ? 1 : 2 * wd * wd + (wd - 2) * 8 * r;
     for (int t = lane; t < total; t += 32) {
@@ -192,7 +209,7 @@ __global__ void __launch_bounds__(256) nn1_query_kernel(const float* __restrict_
       if (!shell_cell(r, t, ddx, ddy, ddz)) continue;
       int cx = qx + ddx, cy = qy + ddy, cz = qz + ddz;
       if (cx < 0 || cy < 0 || cz < 0 || cx >= dx_ || cy >= dy_ || cz >= dz_) continue;
-      int2 ce = __ldg(&cells[(cz * NN1_MAX_DIM + cy) * NN1_MAX_DIM + cx]);
+      int2 ce = __ldg(&cells[nn1_key(cx, cy, cz)]);
       for (int j = ce.x; j < ce.y; ++j) {
         float4 p = __ldg(&sorted[j]);
         double ex = (double)p.x - (double)x, ey = (double)p.y - (double)y, ez = (double)p.z - (double)z;
@@ -214,7 +231,70 @@ __global__ void __launch_bounds__(256) nn1_query_kernel(const float* __restrict_
       }
     }
     double g = fmax(0.0, r * cell + slack - 1e-3 * cell * (r > 0));
-    if (besti != 0x7fffffff && best <= g * g) break;
+    if (besti != 0x7fffffff && best <= g * g) done = true;
+  }
+  // ---- phase 2: coarse shells (8^3 fine cells each).  Lanes test the shell's coarse cells against the current best
+  // through the distance to the cell's box; the warp then scans the surviving cells' points together (contiguous).
+  if (!done) {
+    const int2* coarse = cells + NN1_NCELLS;
+    const int qX = qx >> 3, qY = qy >> 3, qZ = qz >> 3;
+    const int cX = (dx_ + 7) >> 3, cY = (dy_ + 7) >> 3, cZ = (dz_ + 7) >> 3;
+    const int rmaxc = max(cX, max(cY, cZ));
+    const double ccell = cell * NN1_COARSE, eps = 1e-3 * cell;
+    const double ox = (double)h->mn[0], oy = (double)h->mn[1], oz = (double)h->mn[2];
+    double gx = ((double)x - ox) / ccell - qX, gy = ((double)y - oy) / ccell - qY, gz = ((double)z - oz) / ccell - qZ;
+    double cslack = fmin(fmin(fmin(gx, 1.0 - gx), fmin(gy, 1.0 - gy)), fmin(gz, 1.0 - gz));
+    cslack = fmax(0.0, fmin(cslack, 1.0)) * ccell;
+    for (int r = 0; r <= rmaxc; ++r) {
+      const int wd = 2 * r + 1;
+      const int total = r == 0 ? 1 : 2 * wd * wd + (wd - 2) * 8 * r;
+      for (int t0 = 0; t0 < total; t0 += 32) {
+        const int t = t0 + lane;
+        int2 ce = make_int2(0, 0);
+        double lb2 = 1e300;
+        int ddx, ddy, ddz;
+        if (t < total && shell_cell(r, t, ddx, ddy, ddz)) {
+          const int cx = qX + ddx, cy = qY + ddy, cz = qZ + ddz;
+          if (cx >= 0 && cy >= 0 && cz >= 0 && cx < cX && cy < cY && cz < cZ) {
+            ce = __ldg(&coarse[(cz * NN1_CDIM + cy) * NN1_CDIM + cx]);
+            const double lx = ox + cx * ccell, ly = oy + cy * ccell, lz = oz + cz * ccell;
+            const double ax = fmax(0.0, fmax(lx - (double)x, (double)x - (lx + ccell)) - eps);
+            const double ay = fmax(0.0, fmax(ly - (double)y, (double)y - (ly + ccell)) - eps);
+            const double az = fmax(0.0, fmax(lz - (double)z, (double)z - (lz + ccell)) - eps);
+            lb2 = ax * ax + ay * ay + az * az;
+          }
+        }
+        unsigned cand = __ballot_sync(0xffffffffu, ce.y > ce.x && lb2 <= best);
+        while (cand) {
+          const int l = __ffs(cand) - 1;
+          cand &= cand - 1;
+          const int j0 = __shfl_sync(0xffffffffu, ce.x, l), j1 = __shfl_sync(0xffffffffu, ce.y, l);
+          const double clb = __shfl_sync(0xffffffffu, lb2, l);
+          if (clb > best) continue;  // pruned by a cell scanned since the ballot (best is warp-uniform)
+          for (int j = j0 + lane; j < j1; j += 32) {
+            float4 p = __ldg(&sorted[j]);
+            double ex = (double)p.x - (double)x, ey = (double)p.y - (double)y, ez = (double)p.z - (double)z;
+            double d2 = ex * ex + ey * ey + ez * ez;
+            int pi = __float_as_int(p.w);
+            if (d2 < best || (d2 == best && pi < besti)) {
+              best = d2;
+              besti = pi;
+            }
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            double ob = __shfl_xor_sync(0xffffffffu, best, o);
+            int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+            if (ob < best || (ob == best && oi < besti)) {
+              best = ob;
+              besti = oi;
+            }
+          }
+        }
+      }
+      double g = fmax(0.0, r * ccell + cslack - eps * (r > 0) - eps);
+      if (besti != 0x7fffffff && best <= g * g) break;
+    }
   }
   if (lane == 0) nn[i] = besti == 0x7fffffff ? -1 : besti;
 }
@@ -241,7 +321,7 @@ extern "C" int gp_nn1_fill(const float* xyz, int64_t n, const uint8_t* seen, flo
   char* ws = (char*)workspace;
   Nn1Header* h = (Nn1Header*)(ws + L.off_hdr);
   int2* cells = (int2*)(ws + L.off_cells);
-  GP_CUDA(cudaMemsetAsync(cells, 0, sizeof(int2) * (size_t)NN1_MAX_DIM * NN1_MAX_DIM * NN1_MAX_DIM, st));
+  GP_CUDA(cudaMemsetAsync(cells, 0, sizeof(int2) * ((size_t)NN1_NCELLS + NN1_NCOARSE), st));
   nn1_init_kernel<<<1, 1, 0, st>>>(h);
   unsigned grid = (unsigned)((n + 255) / 256);
   nn1_bbox_kernel<<<grid < 1184 ? grid : 1184, 256, 0, st>>>(xyz, n, h);

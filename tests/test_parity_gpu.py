@@ -368,3 +368,33 @@ def test_voxelizer_argument_errors(gp):
         Voxelizer(voxel_size=0.02, use_augmentation=True)
     with pytest.raises(_lib.GeoPurifyError):
         gp.voxelize(torch.zeros((0, 3), device="cuda"), np.eye(4)[:3])
+
+
+# ----------------------------------------------------------------------------- hole fill, far queries
+@pytest.mark.parametrize("case", ["corner", "sparse", "duplicates", "three_state"])
+def test_nn1_fill_matches_bruteforce(gp, case):
+    """1-NN fill against an exact float64 brute force (lowest index on ties), with queries metres away from the
+    nearest seen point (coarse-shell phase), duplicate coordinates (ties) and the 3-state mask."""
+    rng = np.random.default_rng(17)
+    n = 6000
+    xyz = (rng.random((n, 3)) * np.array([5.0, 4.0, 2.7])).astype(np.float32)
+    seen = np.zeros(n, dtype=np.uint8)
+    if case == "corner":
+        seen[(xyz[:, 0] < 0.6) & (xyz[:, 1] < 0.6)] = 1
+    elif case == "sparse":
+        seen[rng.choice(n, 12, replace=False)] = 1
+    elif case == "duplicates":
+        xyz[1000:2000] = xyz[:1000]
+        seen[500:1500] = 1
+    else:
+        seen[:] = 2
+        seen[rng.choice(n, 300, replace=False)] = 1
+        seen[rng.choice(n, 900, replace=False)] = 0
+    x = torch.as_tensor(xyz).cuda()
+    nn = gp.nn1_fill(x, torch.as_tensor(seen).cuda(), 0.05).cpu().numpy()
+    src = np.nonzero(seen == 1)[0]
+    qry = np.nonzero(seen == 0)[0]
+    d = ((xyz[qry].astype(np.float64)[:, None, :] - xyz[src].astype(np.float64)[None, :, :]) ** 2).sum(-1)
+    want = src[np.argmin(d, axis=1)]          # argmin returns the first minimum: lowest source index on ties
+    assert (nn[qry] == want).all(), f"{(nn[qry] != want).sum()} of {len(qry)} differ"
+    assert (nn[src] == src).all()
