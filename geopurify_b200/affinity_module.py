@@ -309,3 +309,65 @@ def run_scene_host(model, h: HostScene, ignore, feat_dtype=torch.bfloat16, feat_
     s = upload_scene(h, feat_dtype, feat_out)
     out = model.run_scene(s, ignore=ignore, want_pred=True)
     return out["pred"].cpu(), out["hist"].cpu()
+
+
+class HostScenePipeline:
+    """`run_scene_host` for a stream of scenes with the copies taken off the critical path: scene i+1 is uploaded on a
+    side stream while scene i runs; results come back through pinned buffers with a second side stream.  Every scene
+    still pays its full host->device and device->host traffic -- the copies overlap the previous / next scene's
+    kernels instead of serialising with them.  Results are identical to calling `run_scene_host` per scene."""
+
+    def __init__(self, model, ignore, feat_dtype=torch.bfloat16, dense=None):
+        self.model, self.ignore, self.feat_dtype = model, ignore, feat_dtype
+        self.dense = (model.lifting != "consensus") if dense is None else dense
+        self.copy_in = torch.cuda.Stream()
+        self.copy_out = torch.cuda.Stream()
+        self._feat = [None, None]     # two dense feature buffers, reused (they are the largest allocation)
+
+    def _upload(self, h, slot):
+        main = torch.cuda.current_stream()
+        with torch.cuda.stream(self.copy_in):
+            self.copy_in.wait_stream(main)            # buffers of slot are free once earlier main-stream work is done
+            fo = self._feat[slot]
+            if self.dense and fo is not None:
+                V, (W, H) = h.t["idmaps"].shape[0], h.image_dim
+                if fo.shape[0] < V or fo.shape[1] != H or fo.shape[2] != W:
+                    fo = None
+                else:
+                    fo = fo[:V]
+            s = upload_scene(h, self.feat_dtype, feat_out=fo, dense=self.dense)
+            if self.dense and (self._feat[slot] is None or self._feat[slot].shape[0] < s.feat.shape[0]):
+                self._feat[slot] = s.feat
+            ev = torch.cuda.Event()
+            ev.record(self.copy_in)
+        return s, ev
+
+    def run(self, hosts):
+        """hosts: sequence of HostScene.  Returns [(pred [N] int64 pinned CPU, hist [3,C] int64 pinned CPU), ...]."""
+        hosts = list(hosts)
+        out, pending = [], []
+        main = torch.cuda.current_stream()
+        nxt = self._upload(hosts[0], 0) if hosts else None
+        for i, h in enumerate(hosts):
+            s, ev = nxt
+            main.wait_event(ev)
+            for t in (s.coords, s.feat, s.depth, s.idmaps, s.tables, s.labels, s.voxel_coords, s.p2v, s.gauss,
+                      s.coords_f32, s.w2c, s.intr):
+                if t is not None:
+                    t.record_stream(main)
+            if i + 1 < len(hosts):
+                nxt = self._upload(hosts[i + 1], (i + 1) & 1)
+            res = self.model.run_scene(s, ignore=self.ignore, want_pred=True)
+            done = torch.cuda.Event()
+            done.record(main)
+            with torch.cuda.stream(self.copy_out):
+                self.copy_out.wait_event(done)
+                pred = torch.empty(res["pred"].shape, dtype=res["pred"].dtype, pin_memory=True)
+                hist = torch.empty(res["hist"].shape, dtype=res["hist"].dtype, pin_memory=True)
+                pred.copy_(res["pred"], non_blocking=True)
+                hist.copy_(res["hist"], non_blocking=True)
+                res["pred"].record_stream(self.copy_out)
+                res["hist"].record_stream(self.copy_out)
+            out.append((pred, hist))
+        self.copy_out.synchronize()
+        return out

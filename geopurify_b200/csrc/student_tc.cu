@@ -464,7 +464,9 @@ __global__ void __launch_bounds__(256) student_reduce_kernel(const float* __rest
 }  // namespace
 
 // ------------------------------------------------------------------ host side
-#define GP_TC_SLAB 32768
+#ifndef GP_TC_SLAB
+#define GP_TC_SLAB 131072
+#endif
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,

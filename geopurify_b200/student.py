@@ -172,7 +172,7 @@ class AffinityPredictor(nn.Module):
             L.check(lib.gp_student_forward_tc(ctypes.byref(desc), L.ptr(flat), L.ptr(self._packed_tc), L.ptr(x),
                                               x.stride(0), L.ptr(nbr27), m, L.ptr(embed), int(normalize), L.ptr(ws),
                                               nb, L.stream()))
-            nslab = (m + 32767) // 32768
+            nslab = (m + 131071) // 131072
             L.count(6 + 2 * nslab * (desc.n_layers - 1) + 2)
             return embed
         nb = lib.gp_student_workspace_bytes(ctypes.byref(desc), m)

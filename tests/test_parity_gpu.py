@@ -398,3 +398,22 @@ def test_nn1_fill_matches_bruteforce(gp, case):
     want = src[np.argmin(d, axis=1)]          # argmin returns the first minimum: lowest source index on ties
     assert (nn[qry] == want).all(), f"{(nn[qry] != want).sum()} of {len(qry)} differ"
     assert (nn[src] == src).all()
+
+
+def test_host_pipeline_equals_per_scene_calls(gp, small_state):
+    """The double-buffered host entry returns exactly what run_scene_host returns scene by scene."""
+    from geopurify_b200.affinity_module import (HostScenePipeline, SonataXAffinityTrainer, host_scene_from_synth,
+                                                run_scene_host)
+    from geopurify_b200.student import AffinityPredictor, load_numpy_state
+    scenes = [synth.make_scene(n_points=n, n_views=5, image_dim=(80, 60), seed=40 + i, room=(2.0, 1.6, 2.0), n_boxes=2,
+                               cut=2, q_range=(4, 12), feat_dim=128, n_classes=7)
+              for i, n in enumerate([9000, 12000, 7000, 12000])]
+    student = load_numpy_state(AffinityPredictor(134, 128, 128), small_state)
+    model = SonataXAffinityTrainer(text_features=scenes[0].text, logit_scale=100.0, student=student, feature_dim=128,
+                                   K=16, n_pool=3, min_visible=50)
+    ign = torch.tensor([scenes[0].ignore_label], dtype=torch.int64, device="cuda")
+    hosts = [host_scene_from_synth(sc) for sc in scenes]
+    want = [run_scene_host(model, h, ign, torch.float32) for h in hosts]
+    got = HostScenePipeline(model, ign, torch.float32).run(hosts)
+    for (p0, h0), (p1, h1) in zip(want, got):
+        assert (p0 == p1).all() and (h0 == h1).all()
