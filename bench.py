@@ -192,7 +192,9 @@ def workload_config(args, sizes=None):
            "views": args.views, "image": "240x320", "feat_dim": 512, "classes": args.classes, "K": args.K,
            "T": args.T, "sharpen": REF_SHARPEN, "feat_dtype_2d": args.feat_dtype,
            "scene_pool_per_rank": args.pool, "parallelism": f"scenes sharded over {args.gpus} GPU(s), 1 rank/GPU",
-           "l2": "inputs larger than L2: each step reads a different scene's 3.9 GB feature maps"}
+           "l2": "inputs larger than L2: each step reads a different scene's 3.9 GB feature maps",
+           "e2e_2d_form": "compact (uint8 id map + fp32 mask-embedding table) crosses PCIe and is lifted directly "
+                          "(gp_lift_mean_idmap); `value` reads resident dense channels-last maps"}
     if sizes is not None:
         cfg["points_per_scene"] = sizes
     return cfg

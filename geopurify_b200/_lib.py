@@ -37,6 +37,8 @@ _SIGS = {
     "gp_accept_views": (c_int, [_P, c_int, c_int, c_int, _P, _P]),
     "gp_lift_mean_fused": (c_int, [_P, c_int, c_int64, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_double, _P, _P,
                                    c_int, c_int, _P, c_int64, _P, _P]),
+    "gp_lift_mean_idmap": (c_int, [_P, c_int, c_int64, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_double, _P, _P,
+                                   _P, c_int, c_int, c_int, _P, c_int64, _P, _P]),
     "gp_expand_idmap": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, _P, c_int, _P]),
     "gp_lift_mean_pix": (c_int, [_P, c_int64, c_int, c_int, c_int, _P, _P, c_int, c_int, _P, c_int64, _P, _P]),
     "gp_lift_consensus_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int, c_int]),

@@ -197,6 +197,9 @@ class SonataXAffinityTrainer:
         if self.lifting == "consensus":
             lifted, seen = ops.lift_consensus(pix, keep, s.idmaps, s.tables, self.text_features, self.logit_scale,
                                               s.coords_f32, self.fill_cell)
+        elif s.feat is None:      # compact 2-D form only: gather through the id map, no dense map
+            lifted, seen = ops.lift_mean_idmap(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, keep,
+                                               s.idmaps, s.tables)
         else:
             lifted, seen = ops.lift_mean_fused(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, keep,
                                                s.feat)
@@ -319,10 +322,20 @@ class HostScenePipeline:
 
     def __init__(self, model, ignore, feat_dtype=torch.bfloat16, dense=None):
         self.model, self.ignore, self.feat_dtype = model, ignore, feat_dtype
-        self.dense = (model.lifting != "consensus") if dense is None else dense
+        # the compact (id map, table) form is lifted directly; dense=True expands it to [V,H,W,D] maps first
+        self.dense = False if dense is None else dense
         self.copy_in = torch.cuda.Stream()
         self.copy_out = torch.cuda.Stream()
         self._feat = [None, None]     # two dense feature buffers, reused (they are the largest allocation)
+        self._pinned = {}             # result buffers in pinned host memory, grown on demand (cudaHostAlloc is slow)
+
+    def _host_out(self, key, shape, dtype):
+        n = int(np.prod(shape))
+        buf = self._pinned.get(key)
+        if buf is None or buf.numel() < n or buf.dtype != dtype:
+            buf = torch.empty(max(n, 1), dtype=dtype, pin_memory=True)
+            self._pinned[key] = buf
+        return buf[:n].view(shape)
 
     def _upload(self, h, slot):
         main = torch.cuda.current_stream()
@@ -362,8 +375,9 @@ class HostScenePipeline:
             done.record(main)
             with torch.cuda.stream(self.copy_out):
                 self.copy_out.wait_event(done)
-                pred = torch.empty(res["pred"].shape, dtype=res["pred"].dtype, pin_memory=True)
-                hist = torch.empty(res["hist"].shape, dtype=res["hist"].dtype, pin_memory=True)
+                # one pinned staging buffer per scene of the batch, reused by later run() calls
+                pred = self._host_out(("pred", i), res["pred"].shape, res["pred"].dtype)
+                hist = self._host_out(("hist", i), res["hist"].shape, res["hist"].dtype)
                 pred.copy_(res["pred"], non_blocking=True)
                 hist.copy_(res["hist"], non_blocking=True)
                 res["pred"].record_stream(self.copy_out)

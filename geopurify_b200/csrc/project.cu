@@ -296,7 +296,8 @@ __global__ void __launch_bounds__(256) lift_mean_kernel(const void* __restrict__
                                                          double thr, const uint8_t* __restrict__ keep,
                                                          const int32_t* __restrict__ pix_in,
                                                          const void* __restrict__ feat, int D, float* __restrict__ out,
-                                                         int64_t out_stride, uint8_t* __restrict__ seen) {
+                                                         int64_t out_stride, uint8_t* __restrict__ seen,
+                                                         const uint8_t* __restrict__ idmap, int Q) {
   extern __shared__ double smem_d[];
   Cam* cams = (Cam*)smem_d;
   uint8_t* skeep = (uint8_t*)(cams + (FROM_PIX ? 0 : V));
@@ -330,11 +331,14 @@ __global__ void __launch_bounds__(256) lift_mean_kernel(const void* __restrict__
       }
       unsigned b = __ballot_sync(0xffffffffu, p >= 0);
       count += __popc(b);
+      // compact 2-D form: the pixel's row is table[v, idmap[v, pixel]] instead of feat[v, pixel]
+      size_t ri = 0;
+      if (p >= 0) ri = idmap ? (size_t)v * Q + min((int)__ldg(idmap + (size_t)v * hw + p), Q - 1) : (size_t)v * hw + (size_t)p;
       while (b) {
         int src = __ffs(b) - 1;
         b &= b - 1;
-        int pp = __shfl_sync(0xffffffffu, p, src);
-        accumulate_row<NV4, BF16>(feat, (size_t)(v0 + src) * hw + (size_t)pp, D, lane, acc);
+        unsigned long long rr = __shfl_sync(0xffffffffu, (unsigned long long)ri, src);
+        accumulate_row<NV4, BF16>(feat, (size_t)rr, D, lane, acc);
       }
     }
     store_mean<NV4, BF16>(out, out_stride, i, lane, acc, count);
@@ -345,7 +349,8 @@ __global__ void __launch_bounds__(256) lift_mean_kernel(const void* __restrict__
 template <typename CT, int DD, bool FROM_PIX>
 static int launch_lift(const void* coords, int64_t n, const double* w2c, const double* intr, const void* depth, int V,
                        int H, int W, int cut, double thr, const uint8_t* keep, const int32_t* pix, const void* feat,
-                       int feat_dtype, int D, float* out, int64_t out_stride, uint8_t* seen, cudaStream_t st) {
+                       int feat_dtype, int D, float* out, int64_t out_stride, uint8_t* seen, cudaStream_t st,
+                       const uint8_t* idmap = nullptr, int Q = 0) {
   size_t smem = (FROM_PIX ? 0 : sizeof(Cam) * V) + V;
   int64_t warps = n;
   int64_t blocks = (warps + 7) / 8;
@@ -355,7 +360,7 @@ static int launch_lift(const void* coords, int64_t n, const double* w2c, const d
 #define LIFT(NV4, BF)                                                                                        \
   lift_mean_kernel<CT, DD, NV4, BF, FROM_PIX><<<grid, 256, smem, st>>>(coords, n, w2c, intr, depth, V, H, W, \
                                                                        cut, thr, keep, pix, feat, D, out,    \
-                                                                       out_stride, seen)
+                                                                       out_stride, seen, idmap, Q)
   if (feat_dtype == GP_F32) {
     switch (nv4) {
       case 1: LIFT(1, false); break;
@@ -407,6 +412,35 @@ extern "C" int gp_lift_mean_fused(const void* coords, int coords_dtype, int64_t 
 #define GO(CT, DD)                                                                                              \
   return launch_lift<CT, DD, false>(coords, n, w2c, intr, depth, V, H, W, cut, vis_thres, keep, nullptr, feat, \
                                     feat_dtype, D, out, out_stride, seen, st)
+  if (coords_dtype == GP_F64) {
+    if (depth_dtype == 0) GO(double, 0);
+    if (depth_dtype == GP_F64) GO(double, GP_F64);
+    if (depth_dtype == GP_F32) GO(double, GP_F32);
+  } else {
+    if (depth_dtype == 0) GO(float, 0);
+    if (depth_dtype == GP_F64) GO(float, GP_F64);
+    if (depth_dtype == GP_F32) GO(float, GP_F32);
+  }
+#undef GO
+  gp_set_error("lift: depth dtype");
+  return GP_ERR_ARG;
+}
+
+extern "C" int gp_lift_mean_idmap(const void* coords, int coords_dtype, int64_t n, const double* w2c,
+                                  const double* intr, const void* depth, int depth_dtype, int V, int H, int W,
+                                  int cut, double vis_thres, const uint8_t* keep, const uint8_t* idmap,
+                                  const void* table, int table_dtype, int Q, int D, float* out, int64_t out_stride,
+                                  uint8_t* seen, gp_stream_t stream) {
+  int rc = check_lift_common(n, V, H, W, table_dtype, D, out_stride, out);
+  if (rc) return rc;
+  GP_CHECK_ARG(coords_dtype == GP_F32 || coords_dtype == GP_F64, "lift: coords dtype");
+  GP_CHECK_ARG((depth == nullptr) == (depth_dtype == 0), "lift: depth pointer / dtype mismatch");
+  GP_CHECK_ARG(idmap != nullptr && Q >= 1 && Q <= 256, "gp_lift_mean_idmap: idmap / Q");
+  if (n == 0) return GP_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+#define GO(CT, DD)                                                                                               \
+  return launch_lift<CT, DD, false>(coords, n, w2c, intr, depth, V, H, W, cut, vis_thres, keep, nullptr, table, \
+                                    table_dtype, D, out, out_stride, seen, st, idmap, Q)
   if (coords_dtype == GP_F64) {
     if (depth_dtype == 0) GO(double, 0);
     if (depth_dtype == GP_F64) GO(double, GP_F64);

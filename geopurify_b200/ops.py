@@ -85,6 +85,24 @@ def lift_mean_fused(coords, w2c, intr, depth, H, W, cut, vis_thres, keep, feat, 
     return out, seen
 
 
+def lift_mean_idmap(coords, w2c, intr, depth, H, W, cut, vis_thres, keep, idmap_u8, table, out=None, out_stride=None):
+    """A1+A4 fused on the compact 2-D form (idmap [V,H,W] uint8, table [V,Q,D] fp32/bf16): no dense map is built.
+    Returns (out [N,stride] fp32, seen [N] uint8)."""
+    lib = L.load()
+    n, V = coords.shape[0], w2c.shape[0]
+    Q, D = table.shape[1], table.shape[2]
+    if out is None:
+        out_stride = out_stride or D
+        out = torch.empty((n, out_stride), dtype=torch.float32, device=_dev())
+    seen = torch.empty((n,), dtype=torch.uint8, device=_dev())
+    dd = 0 if depth is None else L.dtype_code(depth)
+    L.check(lib.gp_lift_mean_idmap(L.ptr(coords), L.dtype_code(coords), n, L.ptr(w2c), L.ptr(intr), L.ptr(depth), dd,
+                                   V, H, W, cut, float(vis_thres), L.ptr(keep), L.ptr(idmap_u8), L.ptr(table),
+                                   L.dtype_code(table), Q, D, L.ptr(out), out.stride(0), L.ptr(seen), L.stream()))
+    L.count(1)
+    return out, seen
+
+
 def expand_idmap(idmap_u8, table_f32, dtype=torch.bfloat16, out=None):
     """feat[v,h,w,:] = table[v, idmap[v,h,w], :] as a dense channels-last map (the 2-D VLM stand-in)."""
     lib = L.load()

@@ -75,6 +75,15 @@ int gp_lift_mean_fused(const void* coords, int coords_dtype, int64_t n, const do
                        const uint8_t* keep, const void* feat, int feat_dtype, int D, float* out,
                        int64_t out_stride, uint8_t* seen, gp_stream_t stream);
 
+/* ---- A1+A4 fused on the COMPACT 2-D form: the feature of pixel (v, p) is table[v, idmap[v, p], :], so the 3.9 GB
+ * dense maps are never built (the X-Decoder path of the reference never builds them either: it adds mask embeddings
+ * per point, models/affinity_module.py:584-592).  Result is bit-identical to gp_expand_idmap + gp_lift_mean_fused
+ * with float32 maps.   idmap [V,H,W] uint8, table [V,Q,D] float32 or bf16 (table_dtype), Q <= 256 */
+int gp_lift_mean_idmap(const void* coords, int coords_dtype, int64_t n, const double* w2c, const double* intr,
+                       const void* depth, int depth_dtype, int V, int H, int W, int cut, double vis_thres,
+                       const uint8_t* keep, const uint8_t* idmap, const void* table, int table_dtype, int Q, int D,
+                       float* out, int64_t out_stride, uint8_t* seen, gp_stream_t stream);
+
 /* ---- 2-D feature form conversion: feat[v,h,w,:] = table[v, idmap[v,h,w], :] (the per-pixel view of the mask
  * embedding lookup at models/affinity_module.py:584-592; also the synthetic stand-in for the 2-D VLM output).
  *   idmap [V,H,W] uint8, table [V,Q,D] float32, feat (out) [V,H,W,D] float32 or bf16, D % 8 == 0 */

@@ -417,3 +417,14 @@ def test_host_pipeline_equals_per_scene_calls(gp, small_state):
     got = HostScenePipeline(model, ign, torch.float32).run(hosts)
     for (p0, h0), (p1, h1) in zip(want, got):
         assert (p0 == p1).all() and (h0 == h1).all()
+
+
+def test_lift_mean_from_compact_form_equals_dense_fp32(gp, scene_run):
+    """gp_lift_mean_idmap == gp_expand_idmap (fp32) + gp_lift_mean_fused, bit for bit."""
+    sc, model, s = scene_run["sc"], scene_run["model"], scene_run["s"]
+    W, H = sc.image_dim
+    keep = model.last_keep
+    a, sa = gp.lift_mean_fused(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, keep, s.feat)
+    b, sb = gp.lift_mean_idmap(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, keep, s.idmaps, s.tables)
+    assert s.feat.dtype == torch.float32
+    assert torch.equal(a, b) and torch.equal(sa, sb)
