@@ -265,7 +265,9 @@ def pool(f0, D, nbr_sorted, weights, T, tensor_core=None):
     if T == 0:
         return f0
     if tensor_core is None:
-        tensor_core = D == 512
+        # the per-scene plan costs about as much as one row-wise application: it pays off from T = 2
+        # (profiles/r01_sweep_pool_knn.jsonl)
+        tensor_core = D == 512 and T >= 2
     if tensor_core:
         nbp = lib.gp_pool_plan_bytes(m, k)
         plan = _ws(nbp)
