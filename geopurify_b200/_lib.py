@@ -31,6 +31,8 @@ _P = c_void_p
 _SIGS = {
     "gp_version": (c_int, []),
     "gp_last_error": (c_char_p, []),
+    "gp_timing_enable": (c_int, [c_int]),
+    "gp_timing_read": (c_int, [c_int, POINTER(c_double), POINTER(c_int)]),
     "gp_project_views": (c_int, [_P, c_int, c_int64, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_double, _P, _P, _P]),
     "gp_pix_to_mapping": (c_int, [_P, c_int64, c_int, _P, _P]),
     "gp_splat_depth": (c_int, [_P, c_int, c_int64, _P, _P, c_int, c_int, c_int, c_int, _P, _P]),

@@ -10,6 +10,10 @@
 
 void gp_set_error(const char* fmt, ...);
 int gp_l2_normalize_rows(float* x, int64_t rows, int E, cudaStream_t st);  // student.cu
+// capi.cu: optional event timing around the dominant kernels (gp_timing_enable); slot ids below
+enum { GP_T_STUDENT_GEMM = 0, GP_T_STUDENT_REDUCE = 1, GP_T_POOL_APPLY = 2, GP_T_POOL_PLAN = 3 };
+bool gp_timing_begin(int which, cudaStream_t st);
+void gp_timing_end(int which, cudaStream_t st);
 
 #define GP_CHECK_ARG(cond, ...)          \
   do {                                   \

@@ -462,7 +462,9 @@ extern "C" int gp_pool_tc(const float* f0, int64_t stride, int D, const void* pl
     P.fin = planes[t & 1];
     P.out_planes = last ? nullptr : planes[(t + 1) & 1];
     P.out_f32 = last ? out : nullptr;
+    const bool tg = gp_timing_begin(GP_T_POOL_APPLY, st);
     pool_tc_kernel<<<grid, PTHREADS, PSMEM, st>>>(P);
+    if (tg) gp_timing_end(GP_T_POOL_APPLY, st);
     GP_LAUNCH_CHECK();
     pool_rows_planes_kernel<<<P.tiles, 256, 0, st>>>(P.fin, P.ucount, nbr_sorted, weights, m, K, P.out_planes,
                                                      P.out_f32);

@@ -676,9 +676,12 @@ extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weig
       P.cout_total = H;
       P.c = staging;
       P.ldc = H;
+      const bool tg = gp_timing_begin(GP_T_STUDENT_GEMM, st);
       int rc = H == 512 ? launch_gemm<512>(map, P, sm_count, st)
                         : (H == 256 ? launch_gemm<256>(map, P, sm_count, st) : launch_gemm<128>(map, P, sm_count, st));
+      if (tg) gp_timing_end(GP_T_STUDENT_GEMM, st);
       if (rc) return rc;
+      const bool tr = gp_timing_begin(GP_T_STUDENT_REDUCE, st);
       int64_t rows = m - (int64_t)slab * L.S < L.S ? m - (int64_t)slab * L.S : L.S;
       unsigned grid = (unsigned)((rows + 7) / 8);
 #define REDUCE(NV4)                                                                                              \
@@ -688,6 +691,7 @@ extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weig
       else if (H == 256) REDUCE(2);
       else REDUCE(1);
 #undef REDUCE
+      if (tr) gp_timing_end(GP_T_STUDENT_REDUCE, st);
       GP_LAUNCH_CHECK();
     }
     woff += (size_t)27 * 2 * H * in_kp;

@@ -37,6 +37,13 @@ enum { GP_F32 = 1, GP_F64 = 2, GP_BF16 = 3 };
 int gp_version(void);
 const char* gp_last_error(void);
 
+/* Optional measurement hook (off by default, not part of the reference surface): when enabled, CUDA events are
+ * recorded on the launching stream around every launch of the dominant kernels; gp_timing_read synchronises them
+ * and returns the summed duration and the launch count since the last gp_timing_enable.
+ * which: 0 student gather-GEMM, 1 student reduce, 2 pooling application (tcgen05), 3 reserved. */
+int gp_timing_enable(int on);
+int gp_timing_read(int which, double* total_ms, int* launches);
+
 /* ---- A1 + A3: PointCloudToImageMapper.compute_mapping for every view of a scene in one launch
  * (models/utils/fusion_util.py:99-147, Matterport twin :45-82; callers dataset/data_loader_ablation.py:242-253,
  * dataset/data_loader_matterport.py:194-205).  float64 arithmetic in the reference's operation order.

@@ -1,13 +1,16 @@
 #!/bin/bash
-# One GPU visit: parity tests, smoke, bench, ncu launch list, ncu full capture of the top kernels.
+# One GPU visit: parity tests, smoke, bench (ours + reference arm), ncu launch list, ncu full captures of the two
+# dominant kernels.  Outputs land in gpurun_out/; profiles/summarize.py turns them into profiles/rNN_*.txt.
 set -x
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke.log
-timeout 900 python bench.py --steps 8 --warmup 3 > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/bench.log
+timeout 900 python bench.py --steps 12 --warmup 3 > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/bench.log
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.log 2>&1
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/launches.csv \
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/launches.csv \
    python bench.py --steps 1 --warmup 0 --pool 1 --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'gather_gemm_tc_kernel|pool_tc_kernel' -s 10 -c 6 \
-   -o gpurun_out/prof_full -f python bench.py --steps 1 --warmup 0 --pool 1 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
-tail -3 gpurun_out/pytest_gpu.log gpurun_out/smoke.log gpurun_out/bench.log
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'gather_gemm_tc_kernel' -s 3 -c 3 \
+   -o gpurun_out/prof_student -f python bench.py --steps 1 --warmup 0 --pool 1 --no-cpu-baseline > gpurun_out/ncu_student.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'pool_tc_kernel' -s 4 -c 2 \
+   -o gpurun_out/prof_pool -f python bench.py --steps 1 --warmup 0 --pool 1 --no-cpu-baseline > gpurun_out/ncu_pool.log 2>&1
+tail -n 3 gpurun_out/pytest_gpu.log; tail -n 2 gpurun_out/smoke.log; tail -n 2 gpurun_out/bench.log | cut -c1-400
