@@ -55,22 +55,63 @@ __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bflo
 }
 
 // ------------------------------------------------------------------ plan: one CTA per tile
-// dynamic smem: keys[npow2] (sorted in place; the unique prefix is then compacted into the same array)
+// The union of the tile's 128 K neighbour ids is built in a shared-memory hash set (only ~5 % of the entries are
+// distinct), compacted, and only the distinct ids are sorted (bitonic over <= 2048 keys instead of 16384).
+constexpr int PLAN_HASH = 4096;                 // slots; the union is capped at KSTEP_CAP * PK = 2048 ids
+constexpr int PLAN_UCAP = KSTEP_CAP * PK;
+
 __global__ void __launch_bounds__(256) pool_tc_plan_kernel(const int32_t* __restrict__ nbr,
                                                             const float* __restrict__ w, int64_t m, int K, int npow2,
                                                             int32_t* __restrict__ ucount, int32_t* __restrict__ uidx,
                                                             uint8_t* __restrict__ wplan) {
-  extern __shared__ uint32_t keys[];
-  __shared__ int s_warp_cnt[8];
+  __shared__ uint32_t table[PLAN_HASH];
+  __shared__ uint32_t keys[PLAN_UCAP];
+  __shared__ int s_nu, s_over;
+  (void)npow2;
   const int64_t t = blockIdx.x;
   const int64_t row0 = t * PT;
   const int rows = (int)min((int64_t)PT, m - row0);
   const int nent = rows * K;
-  for (int e = threadIdx.x; e < npow2; e += 256) keys[e] = e < nent ? (uint32_t)__ldg(nbr + row0 * K + e) : 0xffffffffu;
+  for (int e = threadIdx.x; e < PLAN_HASH; e += 256) table[e] = 0xffffffffu;
+  if (threadIdx.x == 0) {
+    s_nu = 0;
+    s_over = 0;
+  }
   __syncthreads();
-  for (int k = 2; k <= npow2; k <<= 1)
+  for (int e = threadIdx.x; e < nent; e += 256) {
+    const uint32_t v = (uint32_t)__ldg(nbr + row0 * K + e);
+    uint32_t h = (v * 2654435761u) >> 20;  // 12 bits
+    for (int probe = 0; probe < PLAN_HASH; ++probe) {
+      const uint32_t old = atomicCAS(&table[h], 0xffffffffu, v);
+      if (old == v) break;
+      if (old == 0xffffffffu) {
+        if (atomicAdd(&s_nu, 1) >= PLAN_UCAP) s_over = 1;
+        break;
+      }
+      if (s_over) break;
+      h = (h + 1) & (PLAN_HASH - 1);
+    }
+  }
+  __syncthreads();
+  if (s_over) {  // union larger than the tensor-core path takes: the row-wise kernel serves this tile
+    if (threadIdx.x == 0) ucount[t] = PLAN_UCAP + 1;
+    return;
+  }
+  const int nu = s_nu;
+  __syncthreads();
+  if (threadIdx.x == 0) s_nu = 0;
+  int np2 = 32;
+  while (np2 < nu) np2 <<= 1;
+  for (int e = threadIdx.x; e < np2; e += 256) keys[e] = 0xffffffffu;
+  __syncthreads();
+  for (int e = threadIdx.x; e < PLAN_HASH; e += 256) {
+    const uint32_t v = table[e];
+    if (v != 0xffffffffu) keys[atomicAdd(&s_nu, 1)] = v;
+  }
+  __syncthreads();
+  for (int k = 2; k <= np2; k <<= 1)
     for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int i = threadIdx.x; i < (npow2 >> 1); i += 256) {
+      for (int i = threadIdx.x; i < (np2 >> 1); i += 256) {
         int lo = ((i & ~(j - 1)) << 1) | (i & (j - 1));
         int hi = lo | j;
         uint32_t a = keys[lo], b = keys[hi];
@@ -82,24 +123,6 @@ __global__ void __launch_bounds__(256) pool_tc_plan_kernel(const int32_t* __rest
       }
       __syncthreads();
     }
-  // unique, in place: chunks of 256 entries; positions never overtake the read cursor
-  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
-  int nu = 0;
-  for (int e0 = 0; e0 < nent; e0 += 256) {
-    int e = e0 + threadIdx.x;
-    uint32_t v = e < nent ? keys[e] : 0xffffffffu;
-    bool first = e < nent && (e == 0 || keys[e - 1] != v);
-    unsigned bal = __ballot_sync(0xffffffffu, first);
-    if (lane == 0) s_warp_cnt[wp] = __popc(bal);
-    __syncthreads();
-    int base = nu;
-    for (int i = 0; i < wp; ++i) base += s_warp_cnt[i];
-    int tot = 0;
-    for (int i = 0; i < 8; ++i) tot += s_warp_cnt[i];
-    if (first) keys[base + __popc(bal & ((1u << lane) - 1))] = v;
-    nu += tot;
-    __syncthreads();
-  }
   if (threadIdx.x == 0) ucount[t] = nu;
   const int ksteps = (nu + PK - 1) / PK;
   if (ksteps > KSTEP_CAP) return;  // this tile is served by the row-wise kernel
@@ -401,13 +424,8 @@ extern "C" int gp_pool_plan(const int32_t* nbr_sorted, const float* weights, int
   if (m == 0) return GP_OK;
   int npow2 = 1;
   while (npow2 < PT * K) npow2 <<= 1;
-  static bool configured = false;
-  if (!configured) {
-    GP_CUDA(cudaFuncSetAttribute(pool_tc_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
-    configured = true;
-  }
   char* p = (char*)plan;
-  pool_tc_plan_kernel<<<(unsigned)L.tiles, 256, npow2 * sizeof(uint32_t), (cudaStream_t)stream>>>(
+  pool_tc_plan_kernel<<<(unsigned)L.tiles, 256, 0, (cudaStream_t)stream>>>(
       nbr_sorted, weights, m, K, npow2, (int32_t*)(p + L.off_count), (int32_t*)(p + L.off_uidx),
       (uint8_t*)(p + L.off_w));
   GP_LAUNCH_CHECK();

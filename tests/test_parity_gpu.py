@@ -428,3 +428,18 @@ def test_lift_mean_from_compact_form_equals_dense_fp32(gp, scene_run):
     b, sb = gp.lift_mean_idmap(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres, keep, s.idmaps, s.tables)
     assert s.feat.dtype == torch.float32
     assert torch.equal(a, b) and torch.equal(sa, sb)
+
+
+def test_pool_tensor_core_union_overflow_falls_back_per_tile(gp):
+    """Tiles whose neighbour union exceeds 2048 rows are served by the row-wise kernel inside gp_pool_tc; mixed with
+    compact tiles in one call."""
+    torch.manual_seed(1)
+    m, K, T = 128 * 24, 32, 3
+    nb = torch.randint(0, m, (m, K), device="cuda", dtype=torch.int32)             # scattered: union ~ 128 K
+    local = (torch.arange(m, device="cuda")[:, None] + torch.arange(1, K + 1, device="cuda")[None, :]) % m
+    nb[: 128 * 12] = local[: 128 * 12].int()                                        # compact tiles
+    w = torch.softmax(torch.randn(m, K, device="cuda"), 1).contiguous()
+    f = torch.randn(m, 512, device="cuda") * 0.1
+    a = gp.pool(f, 512, nb.contiguous(), w, T, tensor_core=True)
+    b = gp.pool(f, 512, nb.contiguous(), w, T, tensor_core=False)
+    assert (a - b).abs().max().item() < 2e-5
