@@ -33,6 +33,11 @@ constexpr int NSTAGE = GP_STU_NSTAGE;  // B (weight) stages of K=16
 constexpr int AK = GP_STU_AK;  // K per A chunk: 64- or 128-byte operand rows, SWIZZLE_64B / SWIZZLE_128B
 constexpr int AKS = AK / BK;   // K=16 steps per A chunk
 constexpr int NA = GP_STU_NA;  // A chunk buffers
+#ifndef GP_STU_CL
+#define GP_STU_CL 1
+#endif
+constexpr int CL = GP_STU_CL;  // CTAs per cluster.  2: tiles of one kernel offset run in lockstep and share W_o by TMA
+                               // multicast -- parity-green but no faster on B200 (12.27 vs 12.19 ms/scene), kept as an option
 constexpr int ALAG = 1;        // A chunks in flight per gather thread besides the one being issued
 constexpr int EPI_LD = 36;     // floats per staged row in the epilogue transpose buffer (16-byte aligned, conflict-free)
 constexpr int NTHREADS = 384;  // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue, 8-11 A gather
@@ -89,8 +94,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
   uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ntiles = P.ntiles_dev ? *P.ntiles_dev : P.ntiles_host;
+  const int ntiles_real = P.ntiles_dev ? *P.ntiles_dev : P.ntiles_host;
+  const int ntiles = (ntiles_real + CL - 1) / CL * CL;  // every CTA of a cluster runs the same number of tiles
   const int ksteps = P.kp / BK;
+  const uint32_t crank = CL > 1 ? tc::cluster_ctarank() : 0;
+  constexpr uint16_t CMASK = (uint16_t)((1u << CL) - 1);
   const int nchunks = (ksteps + AKS - 1) / AKS;
 
   if (threadIdx.x == 0) {
@@ -98,7 +106,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
     tc::tma_prefetch_desc(&wmap);
     for (int s = 0; s < NSTAGE; ++s) {
       tc::mbar_init(&b_full[s], 1);
-      tc::mbar_init(&b_empty[s], 1);
+      tc::mbar_init(&b_empty[s], CL);  // the MMA warp of every CTA in the cluster releases the stage everywhere
     }
     for (int s = 0; s < NA; ++s) {
       tc::mbar_init(&a_full[s], 4);
@@ -111,16 +119,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
   if (warp == 2) tc::tmem_alloc<N>(tmem_slot);
   tc::tc_fence_before();
   __syncthreads();
+  if (CL > 1) tc::cluster_sync_all();  // peers' barriers are initialised before anything is multicast to them
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   auto tile_of = [&](int t) -> TileInfo {
-    if (P.tiles) return P.tiles[t];
+    if (P.tiles) {
+      TileInfo ti = P.tiles[t < ntiles_real ? t : ntiles_real - 1];
+      if (t >= ntiles_real) ti.nrows = 0;
+      return ti;
+    }
     TileInfo ti;
     ti.offset = 0;
     ti.p0 = t * TM;
     int64_t left = P.m_rows - (int64_t)t * TM;
-    ti.nrows = left < TM ? (int)left : TM;
+    ti.nrows = left < TM ? (left > 0 ? (int)left : 0) : TM;
     ti.c_row0 = t * TM;
     return ti;
   };
@@ -138,12 +151,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
           tc::mbar_wait(&b_empty[s], ph ^ 1);
           tc::mbar_arrive_expect_tx(&b_full[s], 2 * S::B_BYTES);
           uint8_t* st = smem + S::B_OFF + s * S::STAGE;
+          constexpr int NBOX = 2 * (N / BOX);  // (plane, 256-row block) boxes of a stage; each CTA fetches NBOX / CL
+          static_assert(NBOX % CL == 0, "boxes per stage must split evenly over the cluster");
 #pragma unroll
-          for (int plane = 0; plane < 2; ++plane)
-#pragma unroll
-            for (int nb = 0; nb < N / BOX; ++nb)
-              tc::tma_load_2d(tc::smem_u32(st + plane * S::B_BYTES + nb * BOX * ROWB), &wmap, 0,
-                              ((ti.offset * 2 + plane) * ksteps + ks) * P.cout_total + nb * BOX, &b_full[s]);
+          for (int bi = 0; bi < NBOX / CL; ++bi) {
+            const int b = (int)crank * (NBOX / CL) + bi;
+            const int plane = b / (N / BOX), nb = b % (N / BOX);
+            const uint32_t dst = tc::smem_u32(st + plane * S::B_BYTES + nb * BOX * ROWB);
+            const int y = ((ti.offset * 2 + plane) * ksteps + ks) * P.cout_total + nb * BOX;
+            if (CL > 1) tc::tma_load_2d_mc(dst, &wmap, 0, y, &b_full[s], CMASK);
+            else tc::tma_load_2d(dst, &wmap, 0, y, &b_full[s]);
+          }
         }
       }
     }
@@ -180,7 +198,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
             tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_lo + boff), IDESC, 1);
             tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_hi + boff), IDESC, 1);
           }
-          tc::umma_commit(&b_empty[s]);
+          if (CL > 1) tc::umma_commit_mc(&b_empty[s], CMASK);
+          else tc::umma_commit(&b_empty[s]);
           if (chunk_end) tc::umma_commit(&a_empty[ab]);
           if (ks == ksteps - 1) tc::umma_commit(tmem_full);
         }
@@ -272,6 +291,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
 
   tc::tc_fence_before();
   __syncthreads();
+  if (CL > 1) tc::cluster_sync_all();  // no CTA leaves while a peer may still multicast into it
   if (warp == 2) tc::tmem_dealloc<N>(tmem_base);
 }
 
@@ -322,7 +342,7 @@ __global__ void tc_build_tiles_kernel(const int32_t* __restrict__ pos, int S, in
       s_t0[o] = run;
       s_p0[o] = p0;
       gtile0[slab * 27 + o] = run;
-      run += (p1 - p0 + TM - 1) / TM;
+      run += ((p1 - p0 + TM - 1) / TM + CL - 1) / CL * CL;  // whole clusters of tiles per kernel offset
     }
     s_t0[27] = run;
     s_p0[27] = pos[group_index(slab, 26, 0, S) + S];
@@ -337,7 +357,7 @@ __global__ void tc_build_tiles_kernel(const int32_t* __restrict__ pos, int S, in
       TileInfo ti;
       ti.offset = o;
       ti.p0 = s_p0[o] + i * TM;
-      ti.nrows = min(TM, cnt - i * TM);
+      ti.nrows = max(0, min(TM, cnt - i * TM));  // 0: padding tile of the cluster group
       ti.c_row0 = (s_t0[o] + i) * TM;
       tt[s_t0[o] + i] = ti;
     }
@@ -517,7 +537,7 @@ static bool tc_layout(const gp_student_desc* d, int64_t m, TcLayout& L) {
   L.S = (int)(m128 < GP_TC_SLAB ? (m128 > 0 ? m128 : TM) : GP_TC_SLAB);
   L.nslab = (int)((m + L.S - 1) / L.S);
   if (L.nslab < 1) L.nslab = 1;
-  L.max_tiles = 27 * (L.S / TM) + 27;
+  L.max_tiles = 27 * (L.S / TM) + 27 * CL;
   L.total = (int64_t)L.nslab * 27 * L.S;
   size_t off = 0;
   auto take = [&](size_t bytes) {
@@ -579,8 +599,21 @@ static int launch_gemm(const CUtensorMap& map, const GemmParams& P, int grid, cu
                                  Smem<N>::TOTAL));
     configured = true;
   }
-  gather_gemm_tc_kernel<N><<<grid, NTHREADS, Smem<N>::TOTAL, st>>>(map, P);
-  GP_LAUNCH_CHECK();
+  grid = grid / CL * CL;
+  if (grid < CL) grid = CL;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid, 1, 1);
+  cfg.blockDim = dim3(NTHREADS, 1, 1);
+  cfg.dynamicSmemBytes = Smem<N>::TOTAL;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  GP_CUDA(cudaLaunchKernelEx(&cfg, gather_gemm_tc_kernel<N>, map, P));
   return GP_OK;
 }
 
