@@ -36,8 +36,9 @@ constexpr int NA = GP_STU_NA;  // A chunk buffers
 #ifndef GP_STU_CL
 #define GP_STU_CL 1
 #endif
-constexpr int CL = GP_STU_CL;  // CTAs per cluster.  2: tiles of one kernel offset run in lockstep and share W_o by TMA
-                               // multicast -- parity-green but no faster on B200 (12.27 vs 12.19 ms/scene), kept as an option
+constexpr int CL = GP_STU_CL;  // 2: CTA pairs (cta_group::2).  Two tiles of one kernel offset form one M = 256 MMA over
+                               // two SMs; each SM gathers its own 128 A rows and ingests only HALF of every W_o slice
+constexpr bool PAIR = CL == 2;
 constexpr int ALAG = 1;        // A chunks in flight per gather thread besides the one being issued
 constexpr int EPI_LD = 36;     // floats per staged row in the epilogue transpose buffer (16-byte aligned, conflict-free)
 constexpr int NTHREADS = 384;  // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue, 8-11 A gather
@@ -53,7 +54,7 @@ template <int N>
 struct Smem {
   static constexpr int A_BYTES = TM * AK * 2;       // per plane per chunk (16 KB)
   static constexpr int A_CHUNK = 2 * A_BYTES;       // hi + lo
-  static constexpr int B_BYTES = N * ROWB;          // per plane
+  static constexpr int B_BYTES = (PAIR ? N / 2 : N) * ROWB;  // per plane (a CTA of a pair holds half of the rows)
   static constexpr int STAGE = 2 * B_BYTES;
   static constexpr int A_OFF = 0;
   static constexpr int B_OFF = NA * A_CHUNK;
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
   const int ntiles = (ntiles_real + CL - 1) / CL * CL;  // every CTA of a cluster runs the same number of tiles
   const int ksteps = P.kp / BK;
   const uint32_t crank = CL > 1 ? tc::cluster_ctarank() : 0;
-  constexpr uint16_t CMASK = (uint16_t)((1u << CL) - 1);
+  [[maybe_unused]] constexpr uint16_t CMASK = (uint16_t)((1u << CL) - 1);
   const int nchunks = (ksteps + AKS - 1) / AKS;
 
   if (threadIdx.x == 0) {
@@ -106,17 +107,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
     tc::tma_prefetch_desc(&wmap);
     for (int s = 0; s < NSTAGE; ++s) {
       tc::mbar_init(&b_full[s], 1);
-      tc::mbar_init(&b_empty[s], CL);  // the MMA warp of every CTA in the cluster releases the stage everywhere
+      tc::mbar_init(&b_empty[s], 1);
     }
     for (int s = 0; s < NA; ++s) {
-      tc::mbar_init(&a_full[s], 4);
+      tc::mbar_init(&a_full[s], PAIR ? 8 : 4);  // pair: the leader's barrier collects both CTAs' gather warps
       tc::mbar_init(&a_empty[s], 1);
     }
     tc::mbar_init(tmem_full, 1);
-    tc::mbar_init(tmem_empty, 4);
+    tc::mbar_init(tmem_empty, PAIR ? 8 : 4);
     tc::fence_barrier_init();
   }
-  if (warp == 2) tc::tmem_alloc<N>(tmem_slot);
+  if (warp == 2) {
+    if (PAIR) tc::tmem_alloc2<N>(tmem_slot);
+    else tc::tmem_alloc<N>(tmem_slot);
+  }
   tc::tc_fence_before();
   __syncthreads();
   if (CL > 1) tc::cluster_sync_all();  // peers' barriers are initialised before anything is multicast to them
@@ -142,35 +146,43 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
     // ===================== TMA producer: W_o^T[k0:k0+16] hi + lo for all N outputs =====================
     if (lane == 0) {
       uint32_t it = 0;
-      constexpr int BOX = N < 256 ? N : 256;
+      [[maybe_unused]] constexpr int BOX = N < 256 ? N : 256;
       for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
         const TileInfo ti = tile_of(t);
         for (int ks = 0; ks < ksteps; ++ks, ++it) {
           const int s = it % NSTAGE;
           const uint32_t ph = (it / NSTAGE) & 1;
           tc::mbar_wait(&b_empty[s], ph ^ 1);
-          tc::mbar_arrive_expect_tx(&b_full[s], 2 * S::B_BYTES);
           uint8_t* st = smem + S::B_OFF + s * S::STAGE;
-          constexpr int NBOX = 2 * (N / BOX);  // (plane, 256-row block) boxes of a stage; each CTA fetches NBOX / CL
-          static_assert(NBOX % CL == 0, "boxes per stage must split evenly over the cluster");
+          if constexpr (PAIR) {
+            // leader: expect both CTAs' halves; every CTA fetches the N/2 rows it feeds to each N = UN instruction
+            constexpr int UNP = N < 256 ? N : 256, HALF = UNP / 2;
+            if (crank == 0) tc::mbar_arrive_expect_tx(&b_full[s], 2 * S::STAGE);
 #pragma unroll
-          for (int bi = 0; bi < NBOX / CL; ++bi) {
-            const int b = (int)crank * (NBOX / CL) + bi;
-            const int plane = b / (N / BOX), nb = b % (N / BOX);
-            const uint32_t dst = tc::smem_u32(st + plane * S::B_BYTES + nb * BOX * ROWB);
-            const int y = ((ti.offset * 2 + plane) * ksteps + ks) * P.cout_total + nb * BOX;
-            if (CL > 1) tc::tma_load_2d_mc(dst, &wmap, 0, y, &b_full[s], CMASK);
-            else tc::tma_load_2d(dst, &wmap, 0, y, &b_full[s]);
+            for (int plane = 0; plane < 2; ++plane)
+#pragma unroll
+              for (int h = 0; h < N / UNP; ++h)
+                tc::tma_load_2d_2sm(tc::smem_u32(st + plane * S::B_BYTES + h * HALF * ROWB), &wmap, 0,
+                                    ((ti.offset * 2 + plane) * ksteps + ks) * P.cout_total + h * UNP + (int)crank * HALF,
+                                    &b_full[s]);
+          } else {
+            tc::mbar_arrive_expect_tx(&b_full[s], 2 * S::B_BYTES);
+#pragma unroll
+            for (int plane = 0; plane < 2; ++plane)
+#pragma unroll
+              for (int nb = 0; nb < N / BOX; ++nb)
+                tc::tma_load_2d(tc::smem_u32(st + plane * S::B_BYTES + nb * BOX * ROWB), &wmap, 0,
+                                ((ti.offset * 2 + plane) * ksteps + ks) * P.cout_total + nb * BOX, &b_full[s]);
           }
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
+  } else if (warp == 1 && (!PAIR || crank == 0)) {
+    // ===================== MMA issuer (pair mode: the leader CTA issues for both SMs) =====================
     constexpr uint64_t DB = tc::umma_desc_kmajor_base<ROWB>();
     constexpr uint64_t DA = tc::umma_desc_kmajor_base<AK * 2>();
     constexpr int UN = N < 256 ? N : 256;
-    constexpr uint32_t IDESC = tc::umma_idesc_bf16(TM, UN);
+    constexpr uint32_t IDESC = tc::umma_idesc_bf16(PAIR ? 2 * TM : TM, UN);
     uint32_t it = 0, ac = 0, tcount = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
       tc::mbar_wait(tmem_empty, (tcount & 1) ^ 1);
@@ -192,16 +204,27 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
 #pragma unroll
           for (int h = 0; h < N / UN; ++h) {
             const uint32_t d = tmem_base + h * UN;
-            const uint32_t boff = h * UN * ROWB;
+            const uint32_t boff = h * (PAIR ? UN / 2 : UN) * ROWB;
             // small terms first, then the leading product
-            tc::umma_bf16(d, tc::umma_desc(DA, a_lo), tc::umma_desc(DB, b_hi + boff), IDESC, ks > 0);
-            tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_lo + boff), IDESC, 1);
-            tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_hi + boff), IDESC, 1);
+            if constexpr (PAIR) {
+              tc::umma_bf16_2sm(d, tc::umma_desc(DA, a_lo), tc::umma_desc(DB, b_hi + boff), IDESC, ks > 0);
+              tc::umma_bf16_2sm(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_lo + boff), IDESC, 1);
+              tc::umma_bf16_2sm(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_hi + boff), IDESC, 1);
+            } else {
+              tc::umma_bf16(d, tc::umma_desc(DA, a_lo), tc::umma_desc(DB, b_hi + boff), IDESC, ks > 0);
+              tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_lo + boff), IDESC, 1);
+              tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_hi + boff), IDESC, 1);
+            }
           }
-          if (CL > 1) tc::umma_commit_mc(&b_empty[s], CMASK);
-          else tc::umma_commit(&b_empty[s]);
-          if (chunk_end) tc::umma_commit(&a_empty[ab]);
-          if (ks == ksteps - 1) tc::umma_commit(tmem_full);
+          if constexpr (PAIR) {  // the same barrier offset in both CTAs
+            tc::umma_commit_2sm(&b_empty[s], CMASK);
+            if (chunk_end) tc::umma_commit_2sm(&a_empty[ab], CMASK);
+            if (ks == ksteps - 1) tc::umma_commit_2sm(tmem_full, CMASK);
+          } else {
+            tc::umma_commit(&b_empty[s]);
+            if (chunk_end) tc::umma_commit(&a_empty[ab]);
+            if (ks == ksteps - 1) tc::umma_commit(tmem_full);
+          }
         }
         __syncwarp();
         if (chunk_end) ++ac;
@@ -225,7 +248,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
         if (ch == N / 32 - 1) {  // accumulator fully read: the next tile's MMAs may start
           tc::tc_fence_before();
           __syncwarp();
-          if (lane == 0) tc::mbar_arrive(tmem_empty);
+          if (lane == 0) {
+            if (PAIR && crank != 0) tc::mbar_arrive_cluster(tmem_empty, 0);
+            else tc::mbar_arrive(tmem_empty);
+          }
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j)
@@ -277,7 +303,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
           tc::cp_async_wait<ALAG>();
           tc::fence_proxy_async();
           __syncwarp();
-          if (lane == 0) tc::mbar_arrive(&a_full[signalled % NA]);
+          if (lane == 0) {
+            if (PAIR && crank != 0) tc::mbar_arrive_cluster(&a_full[signalled % NA], 0);
+            else tc::mbar_arrive(&a_full[signalled % NA]);
+          }
           ++signalled;
         }
       }
@@ -286,13 +315,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
     tc::fence_proxy_async();
     __syncwarp();
     for (; signalled < ac; ++signalled)
-      if (lane == 0) tc::mbar_arrive(&a_full[signalled % NA]);
+      if (lane == 0) {
+        if (PAIR && crank != 0) tc::mbar_arrive_cluster(&a_full[signalled % NA], 0);
+        else tc::mbar_arrive(&a_full[signalled % NA]);
+      }
   }
 
   tc::tc_fence_before();
   __syncthreads();
-  if (CL > 1) tc::cluster_sync_all();  // no CTA leaves while a peer may still multicast into it
-  if (warp == 2) tc::tmem_dealloc<N>(tmem_base);
+  if (CL > 1) tc::cluster_sync_all();  // no CTA leaves while its peer may still signal it or read its smem
+  if (warp == 2) {
+    if (PAIR) tc::tmem_dealloc2<N>(tmem_base);
+    else tc::tmem_dealloc<N>(tmem_base);
+  }
 }
 
 
@@ -683,7 +718,7 @@ extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weig
   for (int l = 0; l + 1 < d->n_layers; ++l) {
     CUtensorMap map;
     const __nv_bfloat16* wl = (const __nv_bfloat16*)packed + woff;
-    GP_CHECK_ARG(make_weight_map(&map, wl, (int64_t)27 * 2 * H * (in_kp / BK), H < 256 ? H : 256),
+    GP_CHECK_ARG(make_weight_map(&map, wl, (int64_t)27 * 2 * H * (in_kp / BK), (H < 256 ? H : 256) / (PAIR ? 2 : 1)),
                  "gp_student_forward_tc: cuTensorMapEncodeTiled failed (layer %d)", l);
     bool is_res_src = false;
     for (int j = l + 1; j < d->n_layers; ++j) is_res_src |= d->residual_from[j] == l;
@@ -735,7 +770,7 @@ extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weig
   {  // 1^3 output layer: plain GEMM [m, H] x [H, E] straight into `embed`
     const int l = d->n_layers - 1;
     CUtensorMap map;
-    GP_CHECK_ARG(make_weight_map(&map, (const __nv_bfloat16*)packed + woff, (int64_t)2 * E * (H / BK), E),
+    GP_CHECK_ARG(make_weight_map(&map, (const __nv_bfloat16*)packed + woff, (int64_t)2 * E * (H / BK), E / (PAIR ? 2 : 1)),
                  "gp_student_forward_tc: cuTensorMapEncodeTiled failed (output layer)");
     GP_CHECK_ARG(!d->bn[l] && !d->relu[l] && d->residual_from[l] < 0, "gp_student_forward_tc: output layer is linear");
     GemmParams P;
