@@ -69,6 +69,26 @@ def accept_views(counts, min_visible=400, max_visible=2**31 - 1):
     return keep
 
 
+def visible_csr(pix, keep, W, want_pixels=True):
+    """F2: CSR of the visible pairs.  Returns (offsets [V+1] int32 device, point_idx [P], view_idx [P], rows [P],
+    cols [P]) -- one host read for P.  rows / cols are the reference's x_label / y_label."""
+    lib = L.load()
+    V, n = pix.shape
+    cap = V * n
+    off = torch.empty((V + 1,), dtype=torch.int32, device=_dev())
+    pidx = torch.empty((cap,), dtype=torch.int32, device=_dev())
+    vidx = torch.empty((cap,), dtype=torch.int32, device=_dev())
+    rows = torch.empty((cap,), dtype=torch.int32, device=_dev()) if want_pixels else None
+    cols = torch.empty((cap,), dtype=torch.int32, device=_dev()) if want_pixels else None
+    nb = lib.gp_visible_csr_workspace_bytes(n, V)
+    ws = _ws(nb)
+    L.check(lib.gp_visible_csr(L.ptr(pix), L.ptr(keep), n, V, W, L.ptr(off), L.ptr(pidx), L.ptr(vidx), L.ptr(rows),
+                               L.ptr(cols), L.ptr(ws), nb, L.stream()))
+    L.count(4)
+    P = int(off[V].item())
+    return off, pidx[:P], vidx[:P], (rows[:P] if want_pixels else None), (cols[:P] if want_pixels else None)
+
+
 def lift_mean_fused(coords, w2c, intr, depth, H, W, cut, vis_thres, keep, feat, out=None, out_stride=None):
     """A1+A4 fused.  feat [V,H,W,D] fp32/bf16 channels-last.  Returns (out [N,stride] fp32, seen [N] uint8)."""
     lib = L.load()

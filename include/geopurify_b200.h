@@ -70,6 +70,16 @@ int gp_splat_depth(const void* coords, int coords_dtype, int64_t n, const double
 int gp_accept_views(const int32_t* counts, int V, int min_visible, int max_visible, uint8_t* keep,
                     gp_stream_t stream);
 
+/* ---- F2: scene batch assembly (dataset/data_loader_ablation.py:254-288, 348-353; collate :446-459): CSR of the
+ * visible (view, point) pairs in (view, point) order, straight from pix [V,n].
+ *   offsets   (out) [V+1] int32 first pair of every view (views with keep == 0 are empty), offsets[V] = P
+ *   point_idx (out) [>= P] int32 point of every pair;  view_idx / rows / cols (out, may be NULL) [>= P] int32:
+ *   the reference's x_label (row) and y_label (col).  Capacity V*n is always enough; P is offsets[V]. */
+size_t gp_visible_csr_workspace_bytes(int64_t n, int V);
+int gp_visible_csr(const int32_t* pix, const uint8_t* keep, int64_t n, int V, int W, int32_t* offsets,
+                   int32_t* point_idx, int32_t* view_idx, int32_t* rows, int32_t* cols, void* workspace,
+                   size_t workspace_bytes, gp_stream_t stream);
+
 /* ---- A1+A4 fused: project, occlusion-test and gather-mean in one pass (models/affinity_module.py:404-438).
  * One warp per point; cameras in shared memory; 128-bit loads of channels-last feature rows; float32 sum in
  * ascending view order (the reference's index_add_ order).

@@ -443,3 +443,26 @@ def test_pool_tensor_core_union_overflow_falls_back_per_tile(gp):
     a = gp.pool(f, 512, nb.contiguous(), w, T, tensor_core=True)
     b = gp.pool(f, 512, nb.contiguous(), w, T, tensor_core=False)
     assert (a - b).abs().max().item() < 2e-5
+
+
+def test_visible_csr_matches_loader_packing(gp, scene_run):
+    """F2: x_label / y_label / point lists of the kept views, in the loader's order."""
+    sc, model, s, ref = scene_run["sc"], scene_run["model"], scene_run["s"], scene_run["ref"]
+    from oracle import oracle
+    W, H = sc.image_dim
+    pix, _ = gp.project_views(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres)
+    off, pidx, vidx, rows, cols = gp.visible_csr(pix, model.last_keep, W)
+    kept, orows, ocols, opids = oracle.accept_views(ref["mappings"], 50)
+    off = off.cpu().numpy()
+    assert off[-1] == sum(len(p) for p in opids) == pidx.numel()
+    for v in range(sc.n_views):
+        a, b = off[v], off[v + 1]
+        if v in kept:
+            i = kept.index(v)
+            assert (pidx[a:b].cpu().numpy() == opids[i]).all() and (vidx[a:b] == v).all()
+            assert (rows[a:b].cpu().numpy() == orows[i]).all() and (cols[a:b].cpu().numpy() == ocols[i]).all()
+        else:
+            assert a == b
+    # empty input
+    o2, p2, *_ = gp.visible_csr(torch.full((3, 0), -1, dtype=torch.int32, device="cuda"), None, W)
+    assert o2.tolist() == [0, 0, 0, 0] and p2.numel() == 0
