@@ -37,6 +37,7 @@ _SIGS = {
     "gp_pix_to_mapping": (c_int, [_P, c_int64, c_int, _P, _P]),
     "gp_splat_depth": (c_int, [_P, c_int, c_int64, _P, _P, c_int, c_int, c_int, c_int, _P, _P]),
     "gp_accept_views": (c_int, [_P, c_int, c_int, c_int, _P, _P]),
+    "gp_mask_partition": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, c_float, _P, _P, _P]),
     "gp_visible_csr_workspace_bytes": (c_size_t, [c_int64, c_int]),
     "gp_visible_csr": (c_int, [_P, _P, c_int64, c_int, c_int, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
     "gp_lift_mean_fused": (c_int, [_P, c_int, c_int64, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_double, _P, _P,

@@ -69,6 +69,24 @@ def accept_views(counts, min_visible=400, max_visible=2**31 - 1):
     return keep
 
 
+def mask_partition(mask_logits, cls_logits, score_thresh=0.0):
+    """F3: [V,Q,H,W] mask logits + [V,Q,C+1] class logits -> (idmap [V,H,W] uint8 with Q = no mask, scores [V,Q])."""
+    lib = L.load()
+    V, Q, H, W = mask_logits.shape
+    idmap = torch.empty((V, H, W), dtype=torch.uint8, device=_dev())
+    scores = torch.empty((V, Q), dtype=torch.float32, device=_dev())
+    L.check(lib.gp_mask_partition(L.ptr(mask_logits), L.ptr(cls_logits), V, Q, cls_logits.shape[-1], H, W,
+                                  float(score_thresh), L.ptr(idmap), L.ptr(scores), L.stream()))
+    L.count(2)
+    return idmap, scores
+
+
+def mask_table(embeddings):
+    """[V,Q,D] query embeddings -> [V,Q+1,D] table whose last row (index Q = "no mask") is zero."""
+    V, Q, D = embeddings.shape
+    return torch.cat([embeddings.float(), torch.zeros((V, 1, D), dtype=torch.float32, device=embeddings.device)], 1)
+
+
 def visible_csr(pix, keep, W, want_pixels=True):
     """F2: CSR of the visible pairs.  Returns (offsets [V+1] int32 device, point_idx [P], view_idx [P], rows [P],
     cols [P]) -- one host read for P.  rows / cols are the reference's x_label / y_label."""

@@ -70,6 +70,16 @@ int gp_splat_depth(const void* coords, int coords_dtype, int64_t n, const double
 int gp_accept_views(const int32_t* counts, int V, int min_visible, int max_visible, uint8_t* keep,
                     gp_stream_t stream);
 
+/* ---- F3: mask post-processing of the 2-D VLM output (models/affinity_module.py:544-570): panoptic-style partition.
+ *   mask_logits [V,Q,H,W] float32 (already resized to mask_shape), cls_logits [V,Q,C1] float32 (last class =
+ *   background), score_thresh = the reference's scores_keep_thresh (0.0)
+ *   idmap (out) [V,H,W] uint8: arg-max query of the pixel where that query's sigmoid >= 0.5, else Q ("no mask")
+ *   scores (out) [V,Q] float32: max softmax probability over the C1-1 real classes, -1 for dropped queries
+ * The surviving masks are disjoint, so idmap + the query embeddings (with an all-zero row appended at index Q) is
+ * exactly the input of gp_lift_consensus. */
+int gp_mask_partition(const float* mask_logits, const float* cls_logits, int V, int Q, int C1, int H, int W,
+                      float score_thresh, uint8_t* idmap, float* scores, gp_stream_t stream);
+
 /* ---- F2: scene batch assembly (dataset/data_loader_ablation.py:254-288, 348-353; collate :446-459): CSR of the
  * visible (view, point) pairs in (view, point) order, straight from pix [V,n].
  *   offsets   (out) [V+1] int32 first pair of every view (views with keep == 0 are empty), offsets[V] = P

@@ -213,6 +213,36 @@ def lift_consensus(n_points, scene_xyz, view_point_feats, pids, text, logit_scal
     return out, seen
 
 
+# ----------------------------------------------------------------------------- F3
+def mask_partition(mask_logits, cls_logits, score_thresh=0.0):
+    """Panoptic-style mask selection of one view (models/affinity_module.py:544-570), restated with its Python loop.
+    mask_logits [Q,H,W], cls_logits [Q,C+1].  Returns (final_keep_indices in ORIGINAL query numbering,
+    final_masks list of bool [H,W], idmap [H,W] int64 with Q where no final mask covers the pixel)."""
+    mask_logits = torch.as_tensor(mask_logits).float()
+    cls_logits = torch.as_tensor(cls_logits).float()
+    q_total = mask_logits.shape[0]
+    scores, labels = F.softmax(cls_logits, dim=-1)[..., :-1].max(-1)            # :544
+    keep = scores > score_thresh                                                # :546
+    cur_scores = scores[keep]
+    cur_masks = mask_logits[keep].sigmoid()                                     # :549
+    kept_ids = torch.nonzero(keep).flatten()
+    idmap = torch.full(mask_logits.shape[1:], q_total, dtype=torch.long)
+    final_keep, final_masks = [], []
+    if cur_masks.shape[0] == 0:
+        return final_keep, final_masks, idmap
+    cur_prob_masks = cur_scores.view(-1, 1, 1) * cur_masks                      # :557
+    cur_mask_ids = cur_prob_masks.argmax(0)                                     # :558
+    for k in range(cur_scores.shape[0]):                                        # :562-570
+        mask_area = (cur_mask_ids == k).sum().item()
+        original_area = (cur_masks[k] >= 0.5).sum().item()
+        mask = (cur_mask_ids == k) & (cur_masks[k] >= 0.5)
+        if mask_area > 0 and original_area > 0 and mask.sum().item() > 0:
+            final_keep.append(int(kept_ids[k]))
+            final_masks.append(mask)
+            idmap[mask] = int(kept_ids[k])
+    return final_keep, final_masks, idmap
+
+
 # ----------------------------------------------------------------------------- F1
 def fnv_hash_vec(arr):
     """dataset/voxelization_utils.py:6-18: uint64 FNV-1-style key, multiply by the prime then xor, per column."""

@@ -466,3 +466,32 @@ def test_visible_csr_matches_loader_packing(gp, scene_run):
     # empty input
     o2, p2, *_ = gp.visible_csr(torch.full((3, 0), -1, dtype=torch.int32, device="cuda"), None, W)
     assert o2.tolist() == [0, 0, 0, 0] and p2.numel() == 0
+
+
+def test_mask_partition_matches_reference_loop(gp):
+    """F3: the per-pixel id map equals the reference's per-query Python loop; the masks it yields are disjoint and
+    the resulting (idmap, table) lifts like the reference's mask_3d_feature / counter2d (one covering mask)."""
+    from oracle import oracle
+    rng = np.random.default_rng(4)
+    V, Q, C1, H, W, D = 3, 37, 8, 24, 32, 128
+    # smooth blobs so that masks have area; a few queries get background-dominated class logits (dropped or weak)
+    yy, xx = np.mgrid[0:H, 0:W]
+    logits = np.empty((V, Q, H, W), dtype=np.float32)
+    for v in range(V):
+        for q in range(Q):
+            cy, cx, r = rng.uniform(0, H), rng.uniform(0, W), rng.uniform(2, 9)
+            logits[v, q] = 4.0 - ((yy - cy) ** 2 + (xx - cx) ** 2) / r ** 2 * 4.0 + rng.normal(0, 0.3, (H, W))
+    cls = rng.normal(0, 2, (V, Q, C1)).astype(np.float32)
+    cls[:, ::5, -1] += 12.0
+    ml, cl = torch.as_tensor(logits).cuda(), torch.as_tensor(cls).cuda()
+    idmap, scores = gp.mask_partition(ml, cl, 0.0)
+    for v in range(V):
+        keep_ids, masks, want = oracle.mask_partition(logits[v], cls[v], 0.0)
+        got = idmap[v].cpu().numpy().astype(np.int64)
+        assert (got == want.numpy()).all(), f"view {v}: {(got != want.numpy()).sum()} pixels differ"
+        assert sorted(set(got.flatten().tolist()) - {Q}) == sorted(keep_ids)
+        if masks:
+            assert int(torch.stack(masks).sum(0).max()) == 1        # disjoint: counter2d is 0 or 1
+    emb = torch.as_tensor(rng.standard_normal((V, Q, D)).astype(np.float32)).cuda()
+    table = gp.mask_table(emb)
+    assert table.shape == (V, Q + 1, D) and float(table[:, Q].abs().sum()) == 0.0
