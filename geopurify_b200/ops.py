@@ -92,7 +92,7 @@ def visible_csr(pix, keep, W, want_pixels=True):
     cols [P]) -- one host read for P.  rows / cols are the reference's x_label / y_label."""
     lib = L.load()
     V, n = pix.shape
-    cap = V * n
+    cap = max(V * n, 1)
     off = torch.empty((V + 1,), dtype=torch.int32, device=_dev())
     pidx = torch.empty((cap,), dtype=torch.int32, device=_dev())
     vidx = torch.empty((cap,), dtype=torch.int32, device=_dev())
