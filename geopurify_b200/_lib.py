@@ -76,6 +76,8 @@ _SIGS = {
     "gp_gather_rows": (c_int, [_P, c_int64, c_int, _P, c_int64, _P, _P]),
     "gp_logits_workspace_bytes": (c_size_t, [c_int, c_int]),
     "gp_logits_argmax": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, c_float, _P, _P, _P, _P, c_size_t, _P]),
+    "gp_logits_tc_workspace_bytes": (c_size_t, [c_int64, c_int, c_int]),
+    "gp_logits_argmax_tc": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, c_float, _P, _P, _P, c_size_t, _P]),
     "gp_iou_hist": (c_int, [_P, _P, _P, c_int64, _P, c_int, c_int, _P, _P, _P]),
 }
 

@@ -10,6 +10,10 @@
 
 void gp_set_error(const char* fmt, ...);
 int gp_l2_normalize_rows(float* x, int64_t rows, int E, cudaStream_t st);  // student.cu
+// logits.cu: fp32 SIMT logits + argmax on the rows flagged in `only` (fix-up pass of gp_logits_argmax_tc)
+int gp_logits_fix_rows(const float* feat, int64_t stride, int D, int64_t rows, const float* text, int C,
+                       float logit_scale, int32_t* label, uint8_t* zero, const uint8_t* only, void* workspace,
+                       size_t workspace_bytes, cudaStream_t st);
 // capi.cu: optional event timing around the dominant kernels (gp_timing_enable); slot ids below
 enum { GP_T_STUDENT_GEMM = 0, GP_T_STUDENT_REDUCE = 1, GP_T_POOL_APPLY = 2, GP_T_POOL_PLAN = 3 };
 bool gp_timing_begin(int which, cudaStream_t st);

@@ -35,10 +35,12 @@ template <int NV4>
 __global__ void __launch_bounds__(256) logits_argmax_kernel(const float* __restrict__ feat, int64_t stride4,
                                                              int64_t rows, const float* __restrict__ text_n, int C,
                                                              float scale, int32_t* __restrict__ label,
-                                                             uint8_t* __restrict__ zero, float* __restrict__ logits) {
+                                                             uint8_t* __restrict__ zero, float* __restrict__ logits,
+                                                             const uint8_t* __restrict__ only) {
   const int lane = threadIdx.x & 31;
   const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (r >= rows) return;
+  if (only && !only[r]) return;  // fix-up pass of the tensor-core path: only the flagged (near-tie / zero) rows
   const int D4 = NV4 * 32;
   float4 f[NV4];
   float ss = 0.f;
@@ -114,9 +116,28 @@ extern "C" size_t gp_logits_workspace_bytes(int C, int D) {
   return gp_align_up(sizeof(float) * (size_t)C * D);
 }
 
+static int logits_argmax_impl(const float* feat, int64_t stride, int D, int64_t rows, const float* text, int C,
+                              float logit_scale, int32_t* label, uint8_t* zero, float* logits_or_null,
+                              void* workspace, size_t workspace_bytes, const uint8_t* only, gp_stream_t stream);
+
 extern "C" int gp_logits_argmax(const float* feat, int64_t stride, int D, int64_t rows, const float* text, int C,
                                 float logit_scale, int32_t* label, uint8_t* zero, float* logits_or_null,
                                 void* workspace, size_t workspace_bytes, gp_stream_t stream) {
+  return logits_argmax_impl(feat, stride, D, rows, text, C, logit_scale, label, zero, logits_or_null, workspace,
+                            workspace_bytes, nullptr, stream);
+}
+
+// the same fp32 kernel restricted to the rows with only[r] != 0 (labels / zero flags of the other rows untouched)
+int gp_logits_fix_rows(const float* feat, int64_t stride, int D, int64_t rows, const float* text, int C,
+                       float logit_scale, int32_t* label, uint8_t* zero, const uint8_t* only, void* workspace,
+                       size_t workspace_bytes, cudaStream_t st) {
+  return logits_argmax_impl(feat, stride, D, rows, text, C, logit_scale, label, zero, nullptr, workspace,
+                            workspace_bytes, only, (gp_stream_t)st);
+}
+
+static int logits_argmax_impl(const float* feat, int64_t stride, int D, int64_t rows, const float* text, int C,
+                              float logit_scale, int32_t* label, uint8_t* zero, float* logits_or_null,
+                              void* workspace, size_t workspace_bytes, const uint8_t* only, gp_stream_t stream) {
   GP_CHECK_ARG(rows >= 0 && C >= 1, "gp_logits_argmax: bad sizes");
   GP_CHECK_ARG(D > 0 && D % 128 == 0 && D <= 1024, "gp_logits_argmax: D must be a multiple of 128, <= 1024");
   GP_CHECK_ARG(stride % 4 == 0 && stride >= D && ((uintptr_t)feat % 16) == 0, "gp_logits_argmax: feat alignment");
@@ -131,7 +152,7 @@ extern "C" int gp_logits_argmax(const float* feat, int64_t stride, int D, int64_
   if (rows == 0) return GP_OK;
   unsigned grid = (unsigned)((rows + 7) / 8);
 #define GO(NV4) \
-  logits_argmax_kernel<NV4><<<grid, 256, 0, st>>>(feat, stride / 4, rows, tn, C, logit_scale, label, zero, logits_or_null)
+  logits_argmax_kernel<NV4><<<grid, 256, 0, st>>>(feat, stride / 4, rows, tn, C, logit_scale, label, zero, logits_or_null, only)
   switch (D / 128) {
     case 1: GO(1); break;
     case 2: GO(2); break;

@@ -76,6 +76,12 @@ struct GemmParams {
   int cout_total;          // rows per (offset, plane, k-step) block of the pre-tiled weights (= layer cout)
   float* c;                // [c_rows][ldc]
   int64_t ldc;
+  // fused arg-max epilogue (classification): when label_out != nullptr nothing is stored to c
+  int32_t* label_out;      // [m_rows] lowest-index arg-max over the first ncols accumulator columns
+  uint8_t* flag_out;       // [m_rows] 1 if the top-2 margin is below margin_rel * rnorm[row] (fp32 re-evaluation)
+  const float* rnorm;      // [m_rows] row norms of A
+  int ncols;
+  float margin_rel;
 };
 
 template <int N>
@@ -240,6 +246,48 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
       tc::mbar_wait(tmem_full, tcount & 1);
       tc::tc_fence_after();
       const int rows_here = ti.nrows - q * 32;  // valid rows in this warp's quadrant
+      if (P.label_out) {
+        // classification: thread = accumulator row, so the arg-max over the columns is thread-local -- no transpose,
+        // no logits in HBM.  Strict > in ascending column order keeps the lowest class index on ties.
+        float best = -INFINITY, second = -INFINITY;
+        int besti = 0;
+        const int nch = (P.ncols + 31) / 32;
+        for (int ch = 0; ch < N / 32; ++ch) {
+          if (ch < nch) {
+            uint32_t v[32];
+            tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ch * 32, v);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float x = __uint_as_float(v[j]);
+              if (ch * 32 + j < P.ncols) {
+                if (x > best) {
+                  second = best;
+                  best = x;
+                  besti = ch * 32 + j;
+                } else if (x > second) {
+                  second = x;
+                }
+              }
+            }
+          }
+          if (ch == N / 32 - 1) {
+            tc::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+              if (PAIR && crank != 0) tc::mbar_arrive_cluster(tmem_empty, 0);
+              else tc::mbar_arrive(tmem_empty);
+            }
+          }
+        }
+        if (lane < rows_here) {
+          const int64_t row = (int64_t)ti.c_row0 + q * 32 + lane;
+          P.label_out[row] = besti;
+          // !(a > b) also catches NaN accumulators and all-zero rows (margin 0, norm 0)
+          P.flag_out[row] = !((best - second) > P.margin_rel * __ldg(P.rnorm + row)) || !(best > -INFINITY);
+        }
+        continue;
+      }
       float* crow = P.c + ((int64_t)ti.c_row0 + q * 32) * P.ldc;
       for (int ch = 0; ch < N / 32; ++ch) {
         uint32_t v[32];
@@ -732,7 +780,7 @@ extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weig
     const float* residual = d->residual_from[l] >= 0 ? res_src[d->residual_from[l]] : nullptr;
     const float* sc = d->bn[l] ? weights + d->bn_off[l] : nullptr;
     for (int slab = 0; slab < L.nslab; ++slab) {
-      GemmParams P;
+      GemmParams P = {};
       P.a = in;
       P.lda = 2 * (int64_t)in_kp;
       P.kp = in_kp;
@@ -773,7 +821,7 @@ extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weig
     GP_CHECK_ARG(make_weight_map(&map, (const __nv_bfloat16*)packed + woff, (int64_t)2 * E * (H / BK), E / (PAIR ? 2 : 1)),
                  "gp_student_forward_tc: cuTensorMapEncodeTiled failed (output layer)");
     GP_CHECK_ARG(!d->bn[l] && !d->relu[l] && d->residual_from[l] < 0, "gp_student_forward_tc: output layer is linear");
-    GemmParams P;
+    GemmParams P = {};
     P.a = in;
     P.lda = 2 * (int64_t)H;
     P.kp = H;
@@ -794,4 +842,144 @@ extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weig
     if (rc) return rc;
   }
   return GP_OK;
+}
+
+// ------------------------------------------------------------------ A12 on the tensor cores
+// Text-embedding classification as a tcgen05/TMEM GEMM with a fused arg-max epilogue (run/validation.py:413-417).
+// arg-max_c s * <f/|f|, t_c/|t_c|> = arg-max_c <f, t_c/|t_c|> for s > 0, so the rows are not normalised: the kernel
+// computes F[rows, D] x T^[D, C] with the fp32-faithful bf16 hi/lo split (3 MMAs per product, error <= 2^-15 |f|),
+// each epilogue thread owns one accumulator row and keeps (best, second, arg best) over the C columns -- no logits
+// ever reach HBM.  Rows whose top-2 margin is below 2e-4 |f| (near ties, all-zero rows, NaNs) are flagged and
+// re-evaluated by the fp32 SIMT kernel, so the labels are identical to gp_logits_argmax's.
+namespace {
+
+__global__ void __launch_bounds__(256) logits_split_kernel(const float* __restrict__ f, int64_t stride, int D,
+                                                           int64_t rows, __nv_bfloat16* __restrict__ planes,
+                                                           float* __restrict__ rnorm) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  float ss = 0.f;
+  for (int c = lane * 4; c < D; c += 128) {
+    const float4 v = ldg_stream_f4((const float4*)(f + r * stride + c));
+    ss = fmaf(v.x, v.x, ss);
+    ss = fmaf(v.y, v.y, ss);
+    ss = fmaf(v.z, v.z, ss);
+    ss = fmaf(v.w, v.w, ss);
+    __nv_bfloat16 h[4], l[4];
+    split_bf16(v.x, h[0], l[0]);
+    split_bf16(v.y, h[1], l[1]);
+    split_bf16(v.z, h[2], l[2]);
+    split_bf16(v.w, h[3], l[3]);
+    *(uint2*)(planes + r * 2 * D + c) = *(const uint2*)h;
+    *(uint2*)(planes + r * 2 * D + D + c) = *(const uint2*)l;
+  }
+  ss = warp_sum(ss);
+  if (lane == 0) rnorm[r] = sqrtf(ss);
+}
+
+// W[k][c] = text[c][k] / max(|text[c]|, 1e-12) for c < C, 0 for the padding columns; one warp per class
+__global__ void __launch_bounds__(256) text_weights_kernel(const float* __restrict__ text, int C, int D, int cpad,
+                                                           float* __restrict__ w) {
+  const int lane = threadIdx.x & 31;
+  const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (c >= cpad) return;
+  float ss = 0.f;
+  if (c < C)
+    for (int k = lane; k < D; k += 32) ss = fmaf(text[(int64_t)c * D + k], text[(int64_t)c * D + k], ss);
+  ss = warp_sum(ss);
+  const float den = fmaxf(sqrtf(ss), 1e-12f);
+  for (int k = lane; k < D; k += 32) w[(int64_t)k * cpad + c] = c < C ? text[(int64_t)c * D + k] / den : 0.f;
+}
+
+struct LogitsTcLayout {
+  int cpad;
+  size_t off_simt, simt_bytes, off_w, off_packed, off_planes, off_rnorm, off_flags, bytes;
+};
+
+bool logits_tc_layout(int64_t rows, int C, int D, LogitsTcLayout& L) {
+  if (rows < 0 || C < 1 || C > 256 || D < 128 || D % 128 != 0 || D > 1024) return false;
+  L.cpad = C <= 128 ? 128 : 256;
+  size_t off = 0;
+  auto take = [&](size_t b) {
+    size_t o = off;
+    off += gp_align_up(b, 1024);
+    return o;
+  };
+  L.simt_bytes = gp_logits_workspace_bytes(C, D);
+  L.off_simt = take(L.simt_bytes);
+  L.off_w = take(sizeof(float) * (size_t)D * L.cpad);
+  L.off_packed = take(sizeof(__nv_bfloat16) * 2 * (size_t)L.cpad * D);
+  L.off_planes = take(sizeof(__nv_bfloat16) * 2 * (size_t)rows * D);
+  L.off_rnorm = take(sizeof(float) * (size_t)rows);
+  L.off_flags = take((size_t)rows);
+  L.bytes = off;
+  return true;
+}
+
+}  // namespace
+
+extern "C" size_t gp_logits_tc_workspace_bytes(int64_t rows, int C, int D) {
+  LogitsTcLayout L;
+  return logits_tc_layout(rows, C, D, L) ? L.bytes : 0;
+}
+
+extern "C" int gp_logits_argmax_tc(const float* feat, int64_t stride, int D, int64_t rows, const float* text, int C,
+                                   float logit_scale, int32_t* label, uint8_t* zero, void* workspace,
+                                   size_t workspace_bytes, gp_stream_t stream) {
+  LogitsTcLayout L;
+  GP_CHECK_ARG(logits_tc_layout(rows, C, D, L), "gp_logits_argmax_tc: needs 1 <= C <= 256, D a multiple of 128 <= 1024");
+  GP_CHECK_ARG(logit_scale > 0.f, "gp_logits_argmax_tc: logit_scale must be > 0 (the arg-max drops it)");
+  GP_CHECK_ARG(stride % 4 == 0 && stride >= D && ((uintptr_t)feat % 16) == 0, "gp_logits_argmax_tc: feat alignment");
+  GP_CHECK_ARG(((uintptr_t)workspace % 256) == 0 || rows == 0, "gp_logits_argmax_tc: workspace must be 256-byte aligned");
+  if (workspace_bytes < L.bytes) {
+    gp_set_error("gp_logits_argmax_tc: workspace %zu < %zu", workspace_bytes, L.bytes);
+    return GP_ERR_WORKSPACE;
+  }
+  GP_CHECK_ARG(encode_tiled_fn() != nullptr, "gp_logits_argmax_tc: cuTensorMapEncodeTiled unavailable");
+  if (rows == 0) return GP_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  static int sm_count = 0;
+  if (!sm_count) {
+    int dev = 0;
+    GP_CUDA(cudaGetDevice(&dev));
+    GP_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+  }
+  char* ws = (char*)workspace;
+  float* w = (float*)(ws + L.off_w);
+  __nv_bfloat16* packed = (__nv_bfloat16*)(ws + L.off_packed);
+  __nv_bfloat16* planes = (__nv_bfloat16*)(ws + L.off_planes);
+  float* rnorm = (float*)(ws + L.off_rnorm);
+  uint8_t* flags = (uint8_t*)(ws + L.off_flags);
+  text_weights_kernel<<<(L.cpad + 7) / 8, 256, 0, st>>>(text, C, D, L.cpad, w);
+  GP_LAUNCH_CHECK();
+  {
+    int64_t total = (int64_t)L.cpad * D;
+    tc_pack_weights_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(w, 1, D, L.cpad, D, packed);
+    GP_LAUNCH_CHECK();
+  }
+  logits_split_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(feat, stride, D, rows, planes, rnorm);
+  GP_LAUNCH_CHECK();
+  CUtensorMap map;
+  GP_CHECK_ARG(make_weight_map(&map, packed, (int64_t)2 * L.cpad * (D / BK), (L.cpad < 256 ? L.cpad : 256) / (PAIR ? 2 : 1)),
+               "gp_logits_argmax_tc: cuTensorMapEncodeTiled failed");
+  GemmParams P = {};
+  P.a = planes;
+  P.lda = 2 * (int64_t)D;
+  P.kp = D;
+  P.ntiles_host = (int)((rows + TM - 1) / TM);
+  P.m_rows = rows;
+  P.cout_total = L.cpad;
+  P.label_out = label;
+  P.flag_out = flags;
+  P.rnorm = rnorm;
+  P.ncols = C;
+  P.margin_rel = 2e-4f;
+  const int grid = P.ntiles_host < sm_count ? P.ntiles_host : sm_count;
+  int rc = L.cpad == 128 ? launch_gemm<128>(map, P, grid, st) : launch_gemm<256>(map, P, grid, st);
+  if (rc) return rc;
+  if (zero) GP_CUDA(cudaMemsetAsync(zero, 0, (size_t)rows, st));
+  // near ties, all-zero rows and NaNs: the fp32 kernel decides (and sets their zero flags)
+  return gp_logits_fix_rows(feat, stride, D, rows, text, C, logit_scale, label, zero, flags, ws + L.off_simt,
+                            L.simt_bytes, st);
 }

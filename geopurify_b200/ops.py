@@ -335,11 +335,22 @@ def gather_rows(rows, D, index_i32):
     return out
 
 
-def logits_argmax(feat, D, text, logit_scale, want_logits=False, want_zero=True):
+def logits_argmax(feat, D, text, logit_scale, want_logits=False, want_zero=True, tensor_core=None):
+    """A12: (label [rows] int32, zero [rows] uint8 | None, logits [rows,C] | None).  Without `want_logits` the labels
+    come from the tcgen05 GEMM with the fused arg-max epilogue (identical labels, see gp_logits_argmax_tc)."""
     lib = L.load()
     rows, C = feat.shape[0], text.shape[0]
     label = torch.empty((rows,), dtype=torch.int32, device=_dev())
     zero = torch.empty((rows,), dtype=torch.uint8, device=_dev()) if want_zero else None
+    if tensor_core is None:
+        tensor_core = (not want_logits) and C <= 256 and D % 128 == 0 and float(logit_scale) > 0 and rows > 0
+    if tensor_core:
+        nb = lib.gp_logits_tc_workspace_bytes(rows, C, D)
+        ws = _ws(nb)
+        L.check(lib.gp_logits_argmax_tc(L.ptr(feat), feat.stride(0), D, rows, L.ptr(text), C, float(logit_scale),
+                                        L.ptr(label), L.ptr(zero), L.ptr(ws), nb, L.stream()))
+        L.count(6)
+        return label, zero, None
     logits = torch.empty((rows, C), dtype=torch.float32, device=_dev()) if want_logits else None
     nb = lib.gp_logits_workspace_bytes(C, D)
     ws = _ws(nb)

@@ -266,6 +266,15 @@ int gp_logits_argmax(const float* feat, int64_t stride, int D, int64_t rows, con
                      float logit_scale, int32_t* label, uint8_t* zero, float* logits_or_null, void* workspace,
                      size_t workspace_bytes, gp_stream_t stream);
 
+/* ---- A12 on the tensor cores: the same labels from a tcgen05/TMEM GEMM F[rows,D] x T^[D,C] (bf16 hi/lo split, fp32
+ * accumulate) with a fused arg-max epilogue -- no logits in HBM.  Rows whose top-2 margin is below 2e-4 |f| (near ties,
+ * all-zero rows) are re-evaluated by the fp32 kernel of gp_logits_argmax, so both entry points return identical labels.
+ * C <= 256, logit_scale > 0, workspace 256-byte aligned.  zero (may be NULL) as in gp_logits_argmax. */
+size_t gp_logits_tc_workspace_bytes(int64_t rows, int C, int D);
+int gp_logits_argmax_tc(const float* feat, int64_t stride, int D, int64_t rows, const float* text, int C,
+                        float logit_scale, int32_t* label, uint8_t* zero, void* workspace, size_t workspace_bytes,
+                        gp_stream_t stream);
+
 /* ---- A12: intersectionAndUnionGPU (util/util.py:160-177): pred[target in ignore] = ignore, three histograms.
  *   label_rows [rows] int32, index [n] int32 or NULL (pred[i] = label_rows[index[i]] else label_rows[i])
  *   target [n] int64, ignore [n_ignore] int64 (device)

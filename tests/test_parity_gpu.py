@@ -495,3 +495,23 @@ def test_mask_partition_matches_reference_loop(gp):
     emb = torch.as_tensor(rng.standard_normal((V, Q, D)).astype(np.float32)).cuda()
     table = gp.mask_table(emb)
     assert table.shape == (V, Q + 1, D) and float(table[:, Q].abs().sum()) == 0.0
+
+
+@pytest.mark.parametrize("C,D", [(20, 512), (200, 512), (7, 128), (160, 512), (256, 256)])
+def test_logits_tensor_core_labels_identical_to_fp32_kernel(gp, C, D):
+    """tcgen05 GEMM + fused arg-max epilogue (+ fp32 fix-up of flagged rows) == the fp32 SIMT kernel, label for label,
+    including exact ties (duplicated text rows -> lowest index), near ties, all-zero rows and a ragged last tile."""
+    g = torch.Generator(device="cuda").manual_seed(C * 1000 + D)
+    rows = 128 * 41 + 77
+    text = torch.randn(C, D, device="cuda", generator=g)
+    if C >= 7:
+        text[5] = text[2]                                  # exact tie between classes 2 and 5
+        text[6] = text[3] * (1 + 1e-7)                     # near tie
+    feat = torch.randn(rows, D, device="cuda", generator=g) * 0.05
+    feat[::97] = 0.0                                       # all-zero rows
+    feat[1::97] = text[2][None, :] * 0.3                   # rows that hit the exact tie
+    a, za, _ = gp.logits_argmax(feat, D, text, 100.0, want_zero=True, tensor_core=True)
+    b, zb, _ = gp.logits_argmax(feat, D, text, 100.0, want_zero=True, tensor_core=False)
+    assert torch.equal(a, b), f"{int((a != b).sum())} labels differ"
+    assert torch.equal(za, zb) and int(za.sum()) == len(range(0, rows, 97))
+    assert int((a[1::97] == 2).sum()) == a[1::97].numel() or C < 7
