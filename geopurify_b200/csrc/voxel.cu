@@ -168,24 +168,25 @@ extern "C" int gp_kernel_map(const void* index_workspace, int64_t m, int ex, int
 // Element e = lane * 4 + j.  Keys are (d^2 << 32) | original index, so ascending key order is the contract
 // "ascending (d^2, index)".
 typedef unsigned long long u64;
-#define U64_MAX 0xffffffffffffffffull
 
-__device__ __forceinline__ void cswap(u64& a, u64& b, bool asc) {
-  u64 lo = a < b ? a : b, hi = a < b ? b : a;
+template <typename KT>
+__device__ __forceinline__ void cswap(KT& a, KT& b, bool asc) {
+  KT lo = a < b ? a : b, hi = a < b ? b : a;
   a = asc ? lo : hi;
   b = asc ? hi : lo;
 }
 
 // one compare-exchange layer of the network: partner distance `s` elements, block size `k` elements
-__device__ __forceinline__ void bitonic_layer(u64 (&v)[4], int lane, int k, int s) {
+template <typename KT>
+__device__ __forceinline__ void bitonic_layer(KT (&v)[4], int lane, int k, int s) {
   if (s >= 4) {
     int ls = s >> 2;
     bool lower = (lane & ls) == 0;
     bool asc = k >= 128 ? true : ((lane & (k >> 2)) == 0);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      u64 other = __shfl_xor_sync(0xffffffffu, v[j], ls);
-      u64 mn = v[j] < other ? v[j] : other, mx = v[j] < other ? other : v[j];
+      KT other = __shfl_xor_sync(0xffffffffu, v[j], ls);
+      KT mn = v[j] < other ? v[j] : other, mx = v[j] < other ? other : v[j];
       v[j] = (lower == asc) ? mn : mx;
     }
   } else if (s == 2) {
@@ -208,7 +209,8 @@ __device__ __forceinline__ void bitonic_layer(u64 (&v)[4], int lane, int k, int 
   }
 }
 
-__device__ __forceinline__ void bitonic_sort128(u64 (&v)[4], int lane) {
+template <typename KT>
+__device__ __forceinline__ void bitonic_sort128(KT (&v)[4], int lane) {
 #pragma unroll
   for (int k = 2; k <= 128; k <<= 1) {
 #pragma unroll
@@ -216,44 +218,43 @@ __device__ __forceinline__ void bitonic_sort128(u64 (&v)[4], int lane) {
   }
 }
 
-__device__ __forceinline__ void bitonic_merge128(u64 (&v)[4], int lane) {
+template <typename KT>
+__device__ __forceinline__ void bitonic_merge128(KT (&v)[4], int lane) {
 #pragma unroll
   for (int s = 64; s > 0; s >>= 1) bitonic_layer(v, lane, 128, s);
 }
 
-__device__ __forceinline__ u64 topk_element(const u64 (&v)[4], int e) {
+template <typename KT>
+__device__ __forceinline__ KT topk_element(const KT (&v)[4], int e) {
   int j = e & 3;
-  u64 x = j == 0 ? v[0] : (j == 1 ? v[1] : (j == 2 ? v[2] : v[3]));
+  KT x = j == 0 ? v[0] : (j == 1 ? v[1] : (j == 2 ? v[2] : v[3]));
   return __shfl_sync(0xffffffffu, x, e >> 2);
 }
 
 // merge `nbuf` buffered keys (shared memory) into the sorted list
-__device__ __forceinline__ void topk_flush(u64 (&list)[4], const u64* buf, int nbuf, int lane) {
-  u64 b[4];
+template <typename KT>
+__device__ __forceinline__ void topk_flush(KT (&list)[4], const KT* buf, int nbuf, int lane) {
+  KT b[4];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) b[j] = (lane * 4 + j < nbuf) ? buf[lane * 4 + j] : U64_MAX;
+  for (int j = 0; j < 4; ++j) b[j] = (lane * 4 + j < nbuf) ? buf[lane * 4 + j] : (KT)~(KT)0;
   bitonic_sort128(b, lane);
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    u64 rev = __shfl_sync(0xffffffffu, b[3 - j], 31 - lane);  // element 127 - e
+    KT rev = __shfl_sync(0xffffffffu, b[3 - j], 31 - lane);  // element 127 - e
     list[j] = list[j] < rev ? list[j] : rev;
   }
   bitonic_merge128(list, lane);
 }
 
-#define KNN_WARPS 8
-__global__ void __launch_bounds__(KNN_WARPS * 32) knn_grid_kernel(const int4* __restrict__ sorted,
-                                                                   const int2* __restrict__ cells,
-                                                                   const int32_t* __restrict__ rank, int64_t m,
-                                                                   int cx, int cy, int cz, int K,
-                                                                   int32_t* __restrict__ nbr_orig,
-                                                                   int32_t* __restrict__ nbr_sorted) {
-  __shared__ u64 sbuf[KNN_WARPS][128];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  u64* buf = sbuf[warp];
-  const int64_t s = (int64_t)blockIdx.x * KNN_WARPS + warp;
-  if (s >= m) return;
-  const int4 q = sorted[s];
+// One query per warp.  Keys are (d^2 << SHIFT) | original index: ascending key order is "ascending (d^2, index)".
+// KT = uint32 (SHIFT 21: index < 2^21, d^2 < 2^11) halves the shuffle traffic of the bitonic networks; it gives up
+// (returns false, the caller re-runs the query with 64-bit keys) when the search radius would need d^2 >= 2^11.
+template <typename KT, int SHIFT>
+__device__ __forceinline__ bool knn_query(const int4* __restrict__ sorted, const int2* __restrict__ cells, int64_t s,
+                                          const int4 q, int cx, int cy, int cz, int K, KT* buf, int lane,
+                                          KT (&list)[4]) {
+  constexpr KT KMAX = (KT)~(KT)0;
+  constexpr long long D2_LIMIT = sizeof(KT) == 4 ? (1ll << (32 - SHIFT)) - 1 : (1ll << 31);
   const int qcx = q.x >> GP_CELL_SHIFT, qcy = q.y >> GP_CELL_SHIFT, qcz = q.z >> GP_CELL_SHIFT;
   int slack;
   {
@@ -261,8 +262,9 @@ __global__ void __launch_bounds__(KNN_WARPS * 32) knn_grid_kernel(const int4* __
     int a = min(ox, GP_CELL - 1 - ox), b = min(oy, GP_CELL - 1 - oy), c = min(oz, GP_CELL - 1 - oz);
     slack = min(a, min(b, c));
   }
-  u64 list[4] = {U64_MAX, U64_MAX, U64_MAX, U64_MAX};
-  u64 thr = U64_MAX;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) list[j] = KMAX;
+  KT thr = KMAX;
   int nbuf = 0;
   const int rmax = max(cx, max(cy, cz));
   for (int r = 0; r <= rmax; ++r) {
@@ -285,12 +287,13 @@ __global__ void __launch_bounds__(KNN_WARPS * 32) knn_grid_kernel(const int4* __
         int beg = __shfl_sync(0xffffffffu, ce.x, src), end = __shfl_sync(0xffffffffu, ce.y, src);
         for (int j0 = beg; j0 < end; j0 += 32) {
           int j = j0 + lane;
-          u64 key = U64_MAX;
+          KT key = KMAX;
           if (j < end && j != s) {
             int4 c = __ldg(&sorted[j]);
             int dx = c.x - q.x, dy = c.y - q.y, dz = c.z - q.z;
             unsigned d2 = (unsigned)(dx * dx) + (unsigned)(dy * dy) + (unsigned)(dz * dz);
-            key = ((u64)d2 << 32) | (unsigned)c.w;
+            // candidates too far for the key width can only matter if the search runs past D2_LIMIT (-> false below)
+            if ((long long)d2 <= D2_LIMIT - 1) key = ((KT)d2 << SHIFT) | (KT)(unsigned)c.w;
           }
           bool take = key < thr;
           unsigned bal = __ballot_sync(0xffffffffu, take);
@@ -315,15 +318,45 @@ __global__ void __launch_bounds__(KNN_WARPS * 32) knn_grid_kernel(const int4* __
       __syncwarp();
     }
     long long g = (long long)r * GP_CELL + 1 + slack;
-    if (thr != U64_MAX && (long long)(thr >> 32) < g * g) break;
+    if (thr != KMAX && (long long)(thr >> SHIFT) < g * g) return true;
+    if (g * g >= D2_LIMIT) return false;  // the next ring could need distances the key cannot hold
+  }
+  return thr != KMAX || sizeof(KT) == 8;
+}
+
+#define KNN_WARPS 8
+__global__ void __launch_bounds__(KNN_WARPS * 32) knn_grid_kernel(const int4* __restrict__ sorted,
+                                                                   const int2* __restrict__ cells,
+                                                                   const int32_t* __restrict__ rank, int64_t m,
+                                                                   int cx, int cy, int cz, int K,
+                                                                   int32_t* __restrict__ nbr_orig,
+                                                                   int32_t* __restrict__ nbr_sorted) {
+  __shared__ u64 sbuf[KNN_WARPS][128];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t s = (int64_t)blockIdx.x * KNN_WARPS + warp;
+  if (s >= m) return;
+  const int4 q = sorted[s];
+  int orig[4];
+  bool done = false;
+  if (m <= (1ll << 21)) {  // 32-bit keys: 21 index bits, 11 distance bits
+    uint32_t list[4];
+    done = knn_query<uint32_t, 21>(sorted, cells, s, q, cx, cy, cz, K, (uint32_t*)sbuf[warp], lane, list);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) orig[j] = (int)(list[j] & 0x1fffffu);
+  }
+  if (!done) {
+    __syncwarp();
+    u64 list[4];
+    knn_query<u64, 32>(sorted, cells, s, q, cx, cy, cz, K, sbuf[warp], lane, list);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) orig[j] = (int)(list[j] & 0xffffffffu);
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     int e = lane * 4 + j;
     if (e < K) {
-      int orig = (int)(list[j] & 0xffffffffu);
-      if (nbr_orig) nbr_orig[(int64_t)q.w * K + e] = orig;
-      if (nbr_sorted) nbr_sorted[s * K + e] = __ldg(&rank[orig]);
+      if (nbr_orig) nbr_orig[(int64_t)q.w * K + e] = orig[j];
+      if (nbr_sorted) nbr_sorted[s * K + e] = __ldg(&rank[orig[j]]);
     }
   }
 }

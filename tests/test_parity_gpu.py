@@ -515,3 +515,19 @@ def test_logits_tensor_core_labels_identical_to_fp32_kernel(gp, C, D):
     assert torch.equal(a, b), f"{int((a != b).sum())} labels differ"
     assert torch.equal(za, zb) and int(za.sum()) == len(range(0, rows, 97))
     assert int((a[1::97] == 2).sum()) == a[1::97].numel() or C < 7
+
+
+@pytest.mark.parametrize("K", [16, 96])
+def test_knn_sparse_cloud_uses_wide_keys(gp, K):
+    """Voxels tens of cells apart: the K-th distance exceeds what the 32-bit keys hold (d^2 >= 2^11), so queries fall
+    back to the 64-bit path; mixed with a dense clump that stays on the 32-bit path.  Bit-exact vs the C oracle."""
+    from oracle import oracle
+    rng = np.random.default_rng(23)
+    sparse = rng.integers(0, 600, (3000, 3))
+    clump = rng.integers(280, 300, (2500, 3))
+    vox = np.unique(np.concatenate([sparse, clump]), axis=0)
+    vox = vox[rng.permutation(vox.shape[0])].astype(np.int32)
+    idx = gp.VoxelIndex(torch.as_tensor(vox).cuda())
+    got, _ = idx.knn(K, want_orig=True, want_sorted=False)
+    want = oracle.knn_c(vox.astype(np.float64), K)
+    assert (got.cpu().numpy().astype(np.int64) == want).all()
