@@ -157,3 +157,16 @@ def test_oracle_voxelizer_matches_reference_golden(golden_dir, name):
     assert (vc == g["voxel_coords"]).all() and (inds == g["inds"]).all() and (rec == g["inds_reconstruct"]).all()
     assert (vc[rec] == np.floor(np.floor(g["coords"].astype(np.float64) * (1 / float(g["voxel_size"]))) -
                                 np.floor(g["coords"].astype(np.float64) * (1 / float(g["voxel_size"]))).min(0))).all()
+
+
+METRIC_CASES = ["scannet20", "scannet200_two_ignores", "single_point", "all_ignored"]
+
+
+@pytest.mark.parametrize("name", METRIC_CASES)
+def test_oracle_iou_histograms_match_reference_golden(golden_dir, name):
+    """A12 metric: the restatement against outputs of the reference's own intersectionAndUnionGPU
+    (tests/golden/make_golden_metric.py)."""
+    g = np.load(os.path.join(golden_dir, f"metric_{name}.npz"))
+    pred = torch.as_tensor(g["pred"]).clone()
+    i, u, t = oracle.intersection_and_union(pred, torch.as_tensor(g["target"]), int(g["k"]), tuple(g["ignore"].tolist()))
+    assert (np.asarray(i) == g["inter"]).all() and (np.asarray(u) == g["union"]).all() and (np.asarray(t) == g["tgt"]).all()

@@ -531,3 +531,16 @@ def test_knn_sparse_cloud_uses_wide_keys(gp, K):
     got, _ = idx.knn(K, want_orig=True, want_sorted=False)
     want = oracle.knn_c(vox.astype(np.float64), K)
     assert (got.cpu().numpy().astype(np.int64) == want).all()
+
+
+@pytest.mark.parametrize("name", ["scannet20", "scannet200_two_ignores", "single_point", "all_ignored"])
+def test_iou_hist_matches_reference_golden(gp, golden_dir, name):
+    """A12 metric against the reference's own intersectionAndUnionGPU outputs, through the reference-named mirror."""
+    from geopurify_b200.validation import intersectionAndUnionGPU
+    g = np.load(os.path.join(golden_dir, f"metric_{name}.npz"))
+    out = torch.as_tensor(g["pred"]).cuda()
+    i, u, t = intersectionAndUnionGPU(out, torch.as_tensor(g["target"]).cuda(), int(g["k"]), g["ignore"].tolist())
+    assert i.dtype == torch.float32 and i.is_cuda
+    assert (i.cpu().numpy() == g["inter"]).all() and (u.cpu().numpy() == g["union"]).all()
+    assert (t.cpu().numpy() == g["tgt"]).all()
+    assert (out.cpu().numpy() == g["pred_after"]).all()            # the in-place ignore overwrite
