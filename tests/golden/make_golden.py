@@ -106,3 +106,23 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+def intrinsics_golden():
+    """make_intrinsic / adjust_intrinsic of the reference (models/utils/fusion_util.py:7-33) on four camera models
+    -> tests/golden/intrinsics.json (called from main below when run as a script)."""
+    import json
+    ref = load_ref()
+    cases = []
+    for fx, fy, mx, my, src, dst in [(577.870605, 577.870605, 319.5, 239.5, [640, 480], [320, 240]),
+                                     (1170.18, 1170.18, 647.75, 483.75, [1296, 968], [648, 484]),
+                                     (1075.4, 1076.1, 629.7, 522.3, [1280, 1024], [640, 512]),
+                                     (500.0, 510.0, 100.0, 80.0, [200, 160], [200, 160])]:
+        k = ref.make_intrinsic(fx, fy, mx, my)
+        a = ref.adjust_intrinsic(k.copy(), src, dst)
+        cases.append(dict(args=[fx, fy, mx, my], src=src, dst=dst, make=k.tolist(), adjust=np.asarray(a).tolist()))
+    json.dump(cases, open(os.path.join(HERE, "intrinsics.json"), "w"), indent=1)
+
+
+if __name__ == "__main__":
+    intrinsics_golden()

@@ -83,3 +83,17 @@ def test_mapper_intrinsics_rescale_matches_reference_ctor():
     m = PointCloudToImageMapper([320, 240], 0.05, 10, intr)
     assert np.array_equal(m.intrinsics, oracle.mapper_intrinsics(intr, (320, 240)))
     assert m.intrinsics[0, 2] == 160 and m.intrinsics[1, 2] == 120
+
+
+def test_intrinsic_helpers_match_reference_golden():
+    """make_intrinsic / adjust_intrinsic (models/utils/fusion_util.py:7-33) against the reference's own outputs."""
+    import json
+    import numpy as np
+    from geopurify_b200 import fusion_util, synth
+    cases = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "intrinsics.json")))
+    for c in cases:
+        for mod in (fusion_util, synth):
+            k = mod.make_intrinsic(*c["args"])
+            assert (np.asarray(k) == np.asarray(c["make"])).all()
+            a = mod.adjust_intrinsic(np.asarray(k).copy(), c["src"], c["dst"])
+            assert (np.asarray(a) == np.asarray(c["adjust"])).all()
