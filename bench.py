@@ -45,6 +45,9 @@ def parse_args():
     ap.add_argument("--points", type=int, default=0, help="fixed N per scene (0: draw from the ScanNet val sizes)")
     ap.add_argument("--views", type=int, default=50)
     ap.add_argument("--classes", type=int, default=20)
+    ap.add_argument("--image", default="320x240", help="view resolution WxH (Matterport-shaped: 640x512)")
+    ap.add_argument("--vis-thres", type=float, default=0.05, help="occlusion tolerance (Matterport: 0.02)")
+    ap.add_argument("--room", default="", help="room size in metres, e.g. 12x10x3 (default: the 5x4x2.7 ScanNet room)")
     ap.add_argument("--K", type=int, default=REF_K)
     ap.add_argument("--T", type=int, default=REF_T)
     ap.add_argument("--feat-dtype", default="bf16", choices=["bf16", "f32"])
@@ -62,6 +65,19 @@ def peaks():
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
 
 
+def image_dim(args):
+    w, h = (int(x) for x in args.image.lower().split("x"))
+    return (w, h)
+
+
+def scene_kwargs(args):
+    kw = dict(image_dim=image_dim(args), feat_dim=512, n_classes=args.classes, vis_thres=args.vis_thres)
+    if args.room:
+        kw["room"] = tuple(float(x) for x in args.room.lower().split("x"))
+        kw["n_boxes"] = 24
+    return kw
+
+
 def scene_sizes(args, rank):
     from geopurify_b200 import synth
     rng = np.random.default_rng(5557 + 1000 * rank)
@@ -75,8 +91,7 @@ def make_scenes(args, rank):
     from geopurify_b200 import synth
     out = []
     for i, n in enumerate(scene_sizes(args, rank)):
-        out.append(synth.make_scene(n_points=n, n_views=args.views, image_dim=(320, 240), feat_dim=512,
-                                    n_classes=args.classes, seed=5557 + 1000 * rank + i))
+        out.append(synth.make_scene(n_points=n, n_views=args.views, seed=5557 + 1000 * rank + i, **scene_kwargs(args)))
     return out
 
 
@@ -187,12 +202,16 @@ def reference_arm(args):
 
 
 def workload_config(args, sizes=None):
-    cfg = {"workload": "ScanNetV2 val-shaped synthetic scenes (BASELINE.json configs[1]): 50 views 240x320, "
-                       "512-d features, 2 cm voxels, student 518-512x9-128, one scene per step",
-           "views": args.views, "image": "240x320", "feat_dim": 512, "classes": args.classes, "K": args.K,
+    w_, h_ = image_dim(args)
+    default_shape = (w_, h_) == (320, 240) and args.views == 50 and not args.room
+    name = ("ScanNetV2 val-shaped synthetic scenes (BASELINE.json configs[1]): 50 views 240x320, "
+            if default_shape else f"synthetic scenes, {args.views} views {h_}x{w_}, ")
+    cfg = {"workload": name + "512-d features, 2 cm voxels, student 518-512x9-128, one scene per step",
+           "views": args.views, "image": f"{h_}x{w_}", "feat_dim": 512, "classes": args.classes, "K": args.K,
            "T": args.T, "sharpen": REF_SHARPEN, "feat_dtype_2d": args.feat_dtype,
            "scene_pool_per_rank": args.pool, "parallelism": f"scenes sharded over {args.gpus} GPU(s), 1 rank/GPU",
-           "l2": "inputs larger than L2: each step reads a different scene's 3.9 GB feature maps",
+           "l2": "inputs larger than L2: each step reads a different scene's "
+                 f"{args.views * h_ * w_ * 512 * (2 if args.feat_dtype == 'bf16' else 4) / 1e9:.1f} GB feature maps",
            "e2e_2d_form": "compact (uint8 id map + fp32 mask-embedding table) crosses PCIe and is lifted directly "
                           "(gp_lift_mean_idmap); `value` reads resident dense channels-last maps"}
     if sizes is not None:
