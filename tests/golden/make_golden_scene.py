@@ -1,0 +1,158 @@
+"""Golden vectors for the whole inference path from the REFERENCE'S OWN CODE.
+
+Run in the build container only (needs /root/reference):
+
+    python tests/golden/make_golden_scene.py
+
+What executes unmodified from /root/reference:
+  * `models/utils/fusion_util.py:PointCloudToImageMapper.compute_mapping`   (per view, as the loader calls it)
+  * `dataset/voxelizer.py:Voxelizer.voxelize`                                (scene voxels + inds_reconstruct)
+  * `dataset/data_loader_ablation.py:scene_based_collate_fn`                 (the 20-tuple `batch_data`)
+  * `models/affinity_module.py:SonataXAffinityTrainer.evaluate_scene` -> `lift_lseg_features` (gather, mean over
+    views, KDTree fill), scatter-mean, `AffinityPredictor` (the reference's class: layer wiring, BN/ReLU/residual
+    order), normalise, kNN K=96 with the self column dropped, softmax(20 cos), `torch.sparse.mm` x19, point gather.
+What is stood in for (tests/golden/ref_stubs, written from the libraries' documented semantics): MinkowskiEngine
+(SparseTensor / 3^3 convolution / BatchNorm / ReLU), faiss.IndexFlatL2, torch_scatter.scatter_mean; the LSeg network
+is replaced by a table of seeded per-view feature maps (the 2-D VLM is outside the path).  sklearn's KDTree is real.
+The per-view item is assembled as `data_loader_ablation.py:242-392` does (those lines sit inside a file-reading
+method and cannot be called on their own).
+
+Only inputs (or the seeds that make them) and outputs are stored.
+"""
+import collections
+import collections.abc
+import os
+import sys
+
+import numpy as np
+import torch
+
+collections.Sequence = collections.abc.Sequence
+collections.Iterable = collections.abc.Iterable
+sys.dont_write_bytecode = True
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+sys.path.insert(0, "/root/reference")
+import ref_stubs  # noqa: E402
+
+ref_stubs.install()
+from dataset.data_loader_ablation import scene_based_collate_fn  # noqa: E402
+from dataset.voxelizer import Voxelizer  # noqa: E402
+from models.affinity_module import AffinityPredictor, SonataXAffinityTrainer  # noqa: E402
+from models.utils.fusion_util import PointCloudToImageMapper  # noqa: E402
+from geopurify_b200 import synth  # noqa: E402
+
+SCENE = dict(n_points=2500, n_views=6, image_dim=(80, 60), seed=23, room=(2.2, 1.8, 2.2), n_boxes=2, cut=3,
+             q_range=(4, 9), feat_dim=512, n_classes=20)
+STUDENT_SEED = 5557
+ROWS = 384     # rows of the [N,512] outputs stored in full; every row also gets a float64 checksum
+
+
+class TableLSeg:
+    """Stands where `LSeg_MultiEvalModule` stands: returns the next B views' [B,512,H,W] maps."""
+
+    def __init__(self, maps):
+        self.maps, self.cursor = maps, 0
+
+    def eval(self):
+        return self
+
+    def forward(self, x, label_set=""):
+        b = x.shape[0]
+        out = self.maps[self.cursor:self.cursor + b]
+        self.cursor += b
+        return out
+
+
+def view_item(v, sc, mapper, voxelizer, scene_vox, scene_rec):
+    """One dataset item, following dataset/data_loader_ablation.py:242-392."""
+    H, W = sc.image_dim[1], sc.image_dim[0]
+    locs_in = sc.coords.astype(np.float32)
+    labels_in = sc.labels.astype(np.int64)
+    point_features = sc.gauss.astype(np.float32)
+    mapping = np.ones([locs_in.shape[0], 4], dtype=int)
+    mapping[:, 1:4], _ = mapper.compute_mapping(sc.w2c[v].T.copy(), locs_in, sc.depth[v])       # :248-253
+    if mapping[:, 3].sum() == 0:                                                                  # :254
+        return None
+    mask = mapping[:, 3]
+    label_3d = labels_in[mask == 1].copy()
+    feature_3d = point_features[mask == 1].copy()
+    locals_3d = locs_in[mask == 1].copy()
+    unique_map = mapping.copy()
+    locs, feats, _, inds_reconstruct = voxelizer.voxelize(locals_3d, feature_3d, label_3d)       # :324
+    coords = torch.from_numpy(locs).int()
+    coords = torch.cat((torch.ones(coords.shape[0], 1, dtype=torch.int), coords), dim=1)
+    feats = torch.ones(coords.shape[0], 3)
+    x_label = torch.from_numpy(mapping[:, 1][mapping[:, 1] != 0]).long()                          # :348-351
+    y_label = torch.from_numpy(mapping[:, 2][mapping[:, 2] != 0]).long()
+    locals_3d_t = torch.from_numpy(locals_3d).float()
+    locals_3d_t = torch.cat((torch.ones(locals_3d_t.shape[0], 1, dtype=torch.float), locals_3d_t), dim=1)
+    img = torch.zeros(H, W, 3)
+    return (torch.from_numpy(locs_in).float(), torch.from_numpy(scene_vox).float(),
+            torch.from_numpy(scene_rec).long(), torch.from_numpy(labels_in).long(), locals_3d_t, coords, feats,
+            torch.from_numpy(feature_3d).float(), torch.from_numpy(label_3d).long(), torch.zeros(label_3d.shape[0]),
+            torch.zeros(H, W, dtype=torch.long), img, x_label, y_label, torch.from_numpy(mask).bool(),
+            torch.from_numpy(inds_reconstruct).long(), torch.from_numpy(unique_map).long(),
+            torch.from_numpy(mapping), None, torch.from_numpy(point_features).float())
+
+
+def checksum(x):
+    x = x.double()
+    return torch.stack([x.sum(1), (x * x).sum(1)], 1).numpy()
+
+
+def main():
+    sc = synth.make_scene(**SCENE)
+    W, H = sc.image_dim
+    mapper = PointCloudToImageMapper([W, H], sc.vis_thres, sc.cut, sc.intrinsics)
+    voxelizer = Voxelizer(voxel_size=0.02, clip_bound=None, use_augmentation=False)
+    locs_in = sc.coords.astype(np.float32)
+    scene_vox, _, _, scene_rec = voxelizer.voxelize(locs_in, sc.gauss.astype(np.float32), sc.labels.astype(np.int64))
+    items = [view_item(v, sc, mapper, voxelizer, scene_vox, scene_rec) for v in range(sc.n_views)]
+    kept = [v for v, it in enumerate(items) if it is not None]
+    batch_data = scene_based_collate_fn(items)
+
+    maps = torch.stack([torch.from_numpy(sc.dense_map(v)).permute(2, 0, 1) for v in kept])     # [V,512,H,W]
+    t = SonataXAffinityTrainer.__new__(SonataXAffinityTrainer)
+    torch.nn.Module.__init__(t)
+    t.device, t.use_lseg, t.use_ape = "cpu", True, False
+    t.lseg_evaluator, t.lseg_normalize = TableLSeg(maps), (lambda x: x)
+    t.text_features, t.logit_scale = torch.from_numpy(sc.text).float(), torch.tensor(float(sc.logit_scale))
+    student = AffinityPredictor(input_dim=518, embed_dim=128, hidden_dim=512)
+    state = synth.make_student_state(518, 512, 128, seed=STUDENT_SEED)
+    sd = student.state_dict()
+    for k in sd:
+        if k in state:
+            sd[k] = torch.as_tensor(np.asarray(state[k]))
+    missing = [k for k in sd if k not in state and not k.endswith("num_batches_tracked")]
+    assert not missing, missing
+    student.load_state_dict(sd)
+    t.affinity_student = student.eval()
+
+    with torch.no_grad():
+        lifted, _, _ = t.lift_lseg_features(batch_data)
+        t.lseg_evaluator.cursor = 0
+        out = t.evaluate_scene(batch_data)
+    feats = out["scene_features"]
+    rows = np.sort(np.random.default_rng(1).choice(feats.shape[0], ROWS, replace=False))
+    logits = torch.nn.functional.normalize(feats, dim=-1) @ torch.nn.functional.normalize(out["text_features"], dim=-1).t()
+    top2 = logits.topk(2, dim=1).values
+    np.savez_compressed(
+        os.path.join(HERE, "scene_lseg.npz"),
+        scene_kwargs=np.array(repr(SCENE)), student_seed=STUDENT_SEED, kept=np.array(kept),
+        coords=locs_in, coords_checksum=np.float64(sc.coords.astype(np.float64).sum()),
+        voxel_coords=scene_vox.astype(np.int32), inds_reconstruct=scene_rec.astype(np.int64),
+        x_labels=batch_data[12].numpy().astype(np.int32), y_labels=batch_data[13].numpy().astype(np.int32),
+        mask_2ds=batch_data[14].numpy().astype(np.uint8),
+        rows=rows, lifted_rows=lifted[rows].numpy(), lifted_checksum=checksum(lifted),
+        scene_rows=feats[rows].numpy(), scene_checksum=checksum(feats),
+        labels=logits.argmax(1).numpy().astype(np.int32), margin=(top2[:, 0] - top2[:, 1]).numpy(),
+        stubbed=np.array(sorted(set(s.split(".")[0] for s in ref_stubs.stubbed))))
+    print("kept views", kept, "points", feats.shape[0], "voxels", scene_vox.shape[0],
+          "stubbed:", sorted(set(s.split(".")[0] for s in ref_stubs.stubbed)))
+    print("feature range", float(feats.min()), float(feats.max()), "min margin", float((top2[:, 0] - top2[:, 1]).min()))
+
+
+if __name__ == "__main__":
+    main()

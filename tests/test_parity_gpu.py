@@ -322,6 +322,35 @@ def test_lift_consensus_single_view_is_normalised_embedding(gp):
     assert (out[~vis] == 0).all()
 
 
+@pytest.mark.parametrize("zero_frac,seed", [(0.5, 1), (0.9, 2)])
+def test_lift_consensus_many_holes_matches_oracle(gp, zero_frac, seed):
+    """Most masks are "no mask": the per-view fills dominate and reach far (batched grid search vs a KDTree per view)."""
+    from oracle import oracle
+    n, V, H, W, Q, D, C = 6000, 5, 24, 32, 10, 64, 7
+    rng = np.random.default_rng(seed)
+    xyz = (rng.random((n, 3)) * np.array([6.0, 4.0, 2.5])).astype(np.float32)
+    tables = rng.standard_normal((V, Q, D)).astype(np.float32)
+    tables[:, rng.random(Q) < zero_frac, :] = 0.0
+    tables[:, 1, :] = 0.0
+    tables[:, 2, :] = rng.standard_normal((V, D))          # at least one real and one empty mask per view
+    tables[V - 1] = 0.0                                    # a view without any real mask
+    idmap = rng.integers(0, Q, (V, H, W)).astype(np.uint8)
+    pix = rng.integers(0, H * W, (V, n)).astype(np.int32)
+    pix[rng.random((V, n)) < 0.6] = -1
+    pix[:, -50:] = -1                                      # points no view sees
+    text = rng.standard_normal((C, D)).astype(np.float32)
+    pids = [np.nonzero(pix[v] >= 0)[0] for v in range(V)]
+    vpf = [tables[v][idmap[v].reshape(-1)[pix[v][pids[v]]]] for v in range(V)]
+    want, want_seen = oracle.lift_consensus(n, xyz.astype(np.float64), vpf, pids, text, 100.0, feat_dim=D)
+    got, seen = gp.lift_consensus(torch.as_tensor(pix).cuda(), None, torch.as_tensor(idmap).cuda(),
+                                  torch.as_tensor(tables).cuda(), torch.as_tensor(text).cuda(), 100.0,
+                                  torch.as_tensor(xyz).cuda())
+    assert (seen.cpu().numpy().astype(bool) == want_seen.numpy()).all()
+    gp.copy_rows(got, D, gp.nn1_fill(torch.as_tensor(xyz).cuda(), seen))
+    err = (got.cpu() - want).abs().max(1).values
+    assert int((err > 1e-5).sum()) == 0, f"{int((err > 1e-5).sum())} rows differ, max {err.max():.3e}"
+
+
 # ----------------------------------------------------------------------------- F1 voxeliser
 @pytest.mark.parametrize("name", ["surface_f32", "cloud_f64_negative", "single_point", "duplicates", "on_cell_faces"])
 def test_voxelizer_matches_reference_golden(gp, golden_dir, name):
@@ -544,3 +573,73 @@ def test_iou_hist_matches_reference_golden(gp, golden_dir, name):
     assert (i.cpu().numpy() == g["inter"]).all() and (u.cpu().numpy() == g["union"]).all()
     assert (t.cpu().numpy() == g["tgt"]).all()
     assert (out.cpu().numpy() == g["pred_after"]).all()            # the in-place ignore overwrite
+
+
+# ----------------------------------------------------------------------------- whole path vs the reference's own run
+@pytest.fixture(scope="module")
+def reference_scene(golden_dir):
+    """tests/golden/scene_lseg.npz: inputs and outputs of the reference's `evaluate_scene` executed in the build
+    container (make_golden_scene.py); scene and student weights are regenerated from their seeds."""
+    import ast
+    from geopurify_b200 import synth
+    from geopurify_b200.student import AffinityPredictor, load_numpy_state
+    g = np.load(os.path.join(golden_dir, "scene_lseg.npz"))
+    sc = synth.make_scene(**ast.literal_eval(str(g["scene_kwargs"])))
+    assert np.array_equal(sc.coords.astype(np.float32), g["coords"]), "synthetic scene generator drifted from the golden run"
+    sc.voxel_coords = g["voxel_coords"].astype(np.float32)
+    sc.inds_reconstruct = g["inds_reconstruct"].astype(np.int64)
+    student = load_numpy_state(AffinityPredictor(518, 128, 512),
+                               synth.make_student_state(518, 512, 128, seed=int(g["student_seed"])))
+    return g, sc, student
+
+
+def _check_against_reference_run(g, sc, feats):
+    rows = torch.as_tensor(g["rows"]).long()
+    feats = feats.float().cpu()
+    err = (feats[rows] - torch.as_tensor(g["scene_rows"])).abs().max().item()
+    assert err <= 1e-3, err                                  # the north star's tolerance for pooled features
+    assert err <= 2e-5, f"regression: {err:.3e} (measured 1e-6-level error on B200)"
+    x = feats.double()
+    cs = torch.stack([x.sum(1), (x * x).sum(1)], 1).numpy()
+    assert np.allclose(cs, g["scene_checksum"], rtol=1e-3, atol=1e-5)
+    logits = torch.nn.functional.normalize(feats, dim=-1) @ torch.nn.functional.normalize(torch.as_tensor(sc.text), dim=-1).t()
+    sure = g["margin"] > 1e-4
+    assert (logits.argmax(1).numpy()[sure] == g["labels"][sure]).all()
+    return err
+
+
+def test_evaluate_scene_tuple_api_matches_reference_run(gp, reference_scene):
+    """The reference-facing call: the loader's 20-tuple in, `scene_features` out (models/affinity_module.py:1491)."""
+    from geopurify_b200.affinity_module import SonataXAffinityTrainer
+    g, sc, student = reference_scene
+    kept = list(g["kept"])
+    maps = torch.stack([torch.as_tensor(sc.dense_map(v)) for v in kept]).cuda().contiguous()      # [V,H,W,D] float32
+    batch_data = [None] * 20
+    batch_data[0] = torch.as_tensor(g["coords"]).float()
+    batch_data[1] = torch.as_tensor(g["voxel_coords"]).float()
+    batch_data[2] = torch.as_tensor(g["inds_reconstruct"]).long()
+    batch_data[12] = torch.as_tensor(g["x_labels"]).long()
+    batch_data[13] = torch.as_tensor(g["y_labels"]).long()
+    batch_data[14] = torch.as_tensor(g["mask_2ds"]).long()
+    batch_data[19] = torch.as_tensor(sc.gauss).float()
+    model = SonataXAffinityTrainer(text_features=sc.text, logit_scale=sc.logit_scale, student=student,
+                                   view_features=lambda bd: maps)
+    lifted, _, _ = model.lift_lseg_features(tuple(batch_data))
+    rows = torch.as_tensor(g["rows"]).long()
+    assert torch.equal(lifted.cpu()[rows], torch.as_tensor(g["lifted_rows"])), "A4 must be bit-exact"
+    out = model.evaluate_scene(tuple(batch_data))
+    assert out["scene_features"].shape == (g["coords"].shape[0], 512)
+    _check_against_reference_run(g, sc, out["scene_features"])
+
+
+def test_run_scene_matches_reference_run(gp, reference_scene):
+    """The B200-first entry (projection fused into the lifting, per-voxel classification) on the same scene."""
+    from geopurify_b200.affinity_module import SonataXAffinityTrainer, scene_inputs_from_synth
+    g, sc, student = reference_scene
+    model = SonataXAffinityTrainer(text_features=sc.text, logit_scale=sc.logit_scale, student=student, min_visible=1)
+    s = scene_inputs_from_synth(sc, feat_dtype=torch.float32)
+    out = model.run_scene(s, ignore=torch.tensor([sc.ignore_label], dtype=torch.int64, device="cuda"), want_pred=True)
+    feats = gp.gather_rows(out["pooled"], 512, out["p2v_sorted"])
+    _check_against_reference_run(g, sc, feats)
+    sure = (g["margin"] > 1e-4) & (sc.labels != sc.ignore_label)   # `pred` carries the ignore id where the target does
+    assert (out["pred"].cpu().numpy()[sure] == g["labels"][sure]).all()
