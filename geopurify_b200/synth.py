@@ -309,3 +309,30 @@ def scannet_val_size(rng):
     """Draw N from a log-normal fitted to `dataset/scannet_val_metrics.tsv` (min 28k, median 105k, max 302k)."""
     n = int(np.exp(rng.normal(math.log(105_000), 0.42)))
     return int(np.clip(n, 28_000, 302_000))
+
+
+def make_mask_predictions(n_views, n_queries, image_hw, text, feat_dim=512, seed=7):
+    """Seeded stand-in for the X-Decoder head outputs of models/affinity_module.py:519-537, per view:
+    `pred_masks` [V,Q,H,W] float32 logits (blobs; about a fifth of the image stays below 0 for every query = "no
+    mask", and some queries never win a pixel), `pred_logits` [V,Q,C+1] float32, `mask_embed` [V,Q,D] float32
+    (class text embedding + noise).  Everything is computed in float64 and rounded once, so the values are
+    reproducible from the seed alone."""
+    rng = np.random.default_rng(seed)
+    H, W = image_hw
+    C = text.shape[0]
+    yy, xx = np.mgrid[0:H, 0:W].astype(np.float64)
+    masks = np.empty((n_views, n_queries, H, W), dtype=np.float32)
+    logits = np.empty((n_views, n_queries, C + 1), dtype=np.float32)
+    embed = np.empty((n_views, n_queries, feat_dim), dtype=np.float32)
+    for v in range(n_views):
+        for q in range(n_queries):
+            cy, cx = rng.uniform(0, H), rng.uniform(0, W)
+            rad = rng.uniform(0.12, 0.3) * max(H, W)
+            amp = rng.uniform(2.0, 6.0)
+            masks[v, q] = (amp * (1.0 - ((yy - cy) ** 2 + (xx - cx) ** 2) / rad ** 2)).astype(np.float32)
+            cls = int(rng.integers(0, C))
+            row = rng.normal(0.0, 1.0, C + 1)
+            row[cls] += rng.uniform(1.0, 4.0)
+            logits[v, q] = row.astype(np.float32)
+            embed[v, q] = (text[cls].astype(np.float64) + rng.normal(0.0, 0.05, feat_dim)).astype(np.float32)
+    return masks, logits, embed

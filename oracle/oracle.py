@@ -12,13 +12,18 @@ Pinning status
     the reference's own `PointCloudToImageMapper` / `PointCloudToImageMappermatterport`
     (imported from the reference tree by `tests/golden/make_golden.py`; vectors committed
     under `tests/golden/`).
-  * A4-A12: PARITY UNPINNED by the reference (it has no tests, fixtures or golden vectors,
-    and MinkowskiEngine / faiss / torch_scatter are neither vendored nor installable here).
-    These rows restate the reference's torch lines with the same torch calls where they
-    exist on CPU (`F.normalize`, `F.softmax`, `torch.sparse.mm`, `torch.histc`, sklearn
-    `KDTree`) and the published definition of the third-party op otherwise
-    (scatter_mean = sum / count; ME conv = sum over occupied 3^3 offsets of W_d^T x, no bias;
-    faiss IndexFlatL2 = exact L2, ties resolved by lowest index as the north star states).
+  * F1 (voxeliser) and the A12 metric: PINNED by the reference's own `Voxelizer.voxelize` and
+    `intersectionAndUnionGPU` (`tests/golden/make_golden_voxel.py`, `make_golden_metric.py`).
+  * A4-A12, F3: PINNED against runs of the reference's own `SonataXAffinityTrainer.evaluate_scene`,
+    `lift_lseg_features`, `lift_xdecoder_features` and `run/validation.py:validate`
+    (`tests/golden/make_golden_scene.py`; vectors `scene_lseg.npz`, `scene_xdecoder.npz`,
+    `validate_two_scenes.npz`).  In those runs MinkowskiEngine, faiss.IndexFlatL2 and
+    torch_scatter.scatter_mean -- neither vendored nor installable here -- are stood in by
+    definition stubs (`tests/golden/ref_stubs/`): scatter_mean = sum / count; ME conv = sum
+    over occupied 3^3 offsets of W_d^T x, offsets x fastest, no bias; IndexFlatL2 = exact L2,
+    ties by lowest index as the north star states.  The arithmetic INSIDE those three
+    operators therefore rests on their documentation; everything around them is the
+    reference's code.  sklearn `KDTree` is the real library.
 """
 from __future__ import annotations
 

@@ -97,6 +97,22 @@ def view_item(v, sc, mapper, voxelizer, scene_vox, scene_rec):
             torch.from_numpy(mapping), None, torch.from_numpy(point_features).float())
 
 
+class TableXDecoder:
+    """Stands where `self.xdecoder_teacher.model` stands: `forward_seg_all` returns the next view's head outputs
+    (models/affinity_module.py:519 reads pred_logits / pred_masks / mask_embed / text_embed / logit_scale)."""
+
+    def __init__(self, masks, logits, embed, text, logit_scale):
+        self.masks, self.logits, self.embed = masks, logits, embed
+        self.text, self.logit_scale, self.cursor = text, logit_scale, 0
+        self.model = self
+
+    def forward_seg_all(self, inputs):
+        v = self.cursor
+        self.cursor += 1
+        return None, {"pred_logits": self.logits[v:v + 1], "pred_masks": self.masks[v:v + 1],
+                      "mask_embed": self.embed[v:v + 1], "text_embed": self.text, "logit_scale": self.logit_scale}
+
+
 def checksum(x):
     x = x.double()
     return torch.stack([x.sum(1), (x * x).sum(1)], 1).numpy()
@@ -149,9 +165,110 @@ def main():
         scene_rows=feats[rows].numpy(), scene_checksum=checksum(feats),
         labels=logits.argmax(1).numpy().astype(np.int32), margin=(top2[:, 0] - top2[:, 1]).numpy(),
         stubbed=np.array(sorted(set(s.split(".")[0] for s in ref_stubs.stubbed))))
+    validate_case(sc, t, batch_data, out)
+    xdecoder_case(sc, t, batch_data, kept)
     print("kept views", kept, "points", feats.shape[0], "voxels", scene_vox.shape[0],
           "stubbed:", sorted(set(s.split(".")[0] for s in ref_stubs.stubbed)))
     print("feature range", float(feats.min()), float(feats.max()), "min margin", float((top2[:, 0] - top2[:, 1]).min()))
+
+
+ZERO_SEED, ZERO_FRAC = 3, 0.1
+BASE, NOVEL = list(range(0, 12)), list(range(12, 20))
+
+
+def validate_case(sc, trainer, batch_data, first_result):
+    """A12: `run/validation.py:validate(val_loader, model)` executed unmodified over a two-scene loader.  Scene 0 is
+    the scene above (the model's `evaluate_scene` result is the reference trainer's); scene 1 is the same scene with
+    10 % of the feature rows zeroed, which sends those points through the KDTree fill of :421-433 (it searches on
+    `scene_coords[:, 1:4]`, i.e. the y and z columns only).  Module globals the function reads (`args`, `logger`) are
+    set from outside; `intersectionAndUnionGPU` is wrapped to record its arguments and results, and `Tensor.cuda` is
+    the identity while it runs (no GPU here)."""
+    import logging
+    import tempfile
+    import types
+    import run.validation as rv
+    n = first_result["scene_features"].shape[0]
+    zero = np.sort(np.random.default_rng(ZERO_SEED).choice(n, int(ZERO_FRAC * n), replace=False))
+    second = dict(first_result)
+    second["scene_features"] = first_result["scene_features"].clone()
+    second["scene_features"][zero] = 0.0
+    results = [first_result, second]
+
+    class Replay:
+        calls = 0
+
+        def eval(self):
+            return self
+
+        def evaluate_scene(self, batch_data, vis_prefix=None):
+            r = results[self.calls]
+            Replay.calls += 1
+            return {k: (v.clone() if torch.is_tensor(v) else v) for k, v in r.items()}
+
+    class Loader(list):
+        dataset = types.SimpleNamespace(data_paths=["scene0000_00_vh_clean_2.pth", "scene0000_01_vh_clean_2.pth"])
+
+    recorded = []
+    ref_metric = rv.intersectionAndUnionGPU
+
+    def recorder(output, target, k, ignore):
+        i, u, t = ref_metric(output, target, k, ignore)
+        recorded.append((output.clone().numpy(), i.numpy(), u.numpy(), t.numpy()))
+        return i, u, t
+
+    rv.args = types.SimpleNamespace(test_classes=20, test_ignore_label=[sc.ignore_label], multiprocessing_distributed=False,
+                                    category_split=types.SimpleNamespace(base_category=BASE, novel_category=NOVEL))
+    rv.logger = logging.getLogger("reference-validate")
+    rv.intersectionAndUnionGPU = recorder
+    cuda, cwd = torch.Tensor.cuda, os.getcwd()
+    torch.Tensor.cuda = lambda self, *a, **kw: self
+    try:
+        with tempfile.TemporaryDirectory() as tmp:
+            os.chdir(tmp)                                   # validate() creates its visualisation directory in the cwd
+            miou_base, miou_novel = rv.validate(Loader([batch_data, batch_data]), Replay())
+    finally:
+        os.chdir(cwd)
+        torch.Tensor.cuda = cuda
+        rv.intersectionAndUnionGPU = ref_metric
+    assert len(recorded) == 2
+    np.savez_compressed(
+        os.path.join(HERE, "validate_two_scenes.npz"),
+        zero_rows=zero, base=np.array(BASE), novel=np.array(NOVEL), ignore=np.array([sc.ignore_label]),
+        pred=np.stack([r[0] for r in recorded]).astype(np.int32), inter=np.stack([r[1] for r in recorded]),
+        union=np.stack([r[2] for r in recorded]), target=np.stack([r[3] for r in recorded]),
+        miou_base=np.float64(miou_base), miou_novel=np.float64(miou_novel))
+    print("validate(): mIoU base/novel", miou_base, miou_novel, "filled predictions", len(zero))
+
+
+XDEC = dict(n_queries=14, seed=7)
+
+
+def xdecoder_case(sc, t, batch_data, kept):
+    """A5: `lift_xdecoder_features` (models/affinity_module.py:455-714) with the X-Decoder forward replaced by seeded
+    head outputs.  `mappings` is handed over per visible pair: the function indexes it with the per-pair view mask
+    (:504), which the [V*N,4] tensor of `scene_based_collate_fn` would not survive; it is not used afterwards."""
+    import types
+    W, H = sc.image_dim
+    masks, logits, embed = synth.make_mask_predictions(len(kept), XDEC["n_queries"], (H, W), sc.text, 512, XDEC["seed"])
+    t.use_lseg = False
+    t.cfg = types.SimpleNamespace(all_label=list(range(sc.text.shape[0])), mask_shape=(H, W), use_ape=False)
+    t.xdecoder_teacher = TableXDecoder(torch.from_numpy(masks), torch.from_numpy(logits), torch.from_numpy(embed),
+                                       torch.from_numpy(sc.text).float(), torch.tensor(float(sc.logit_scale)))
+    bd = list(batch_data)
+    bd[17] = bd[4].clone()
+    with torch.no_grad():
+        lifted, text_n, scale = t.lift_xdecoder_features(tuple(bd))
+    rows = np.sort(np.random.default_rng(2).choice(lifted.shape[0], ROWS, replace=False))
+    zero_rows = int((lifted.abs().sum(1) == 0).sum())
+    np.savez_compressed(
+        os.path.join(HERE, "scene_xdecoder.npz"),
+        scene_kwargs=np.array(repr(SCENE)), kept=np.array(kept), n_queries=XDEC["n_queries"], mask_seed=XDEC["seed"],
+        coords=sc.coords.astype(np.float32),
+        x_labels=batch_data[12].numpy().astype(np.int32), y_labels=batch_data[13].numpy().astype(np.int32),
+        mask_2ds=batch_data[14].numpy().astype(np.uint8),
+        rows=rows, lifted_rows=lifted[rows].numpy(), lifted_checksum=checksum(lifted),
+        text_normalised_checksum=checksum(text_n))
+    print("xdecoder lifting:", tuple(lifted.shape), "all-zero rows", zero_rows, "logit_scale", float(scale))
 
 
 if __name__ == "__main__":

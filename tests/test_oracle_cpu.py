@@ -186,6 +186,17 @@ def _golden_scene(golden_dir):
     return g, sc, state
 
 
+_ORACLE_RUN = {}
+
+
+def _oracle_run(golden_dir):
+    """oracle.evaluate_scene on the golden scene (15 s on CPU), shared by the tests below."""
+    if golden_dir not in _ORACLE_RUN:
+        g, sc, state = _golden_scene(golden_dir)
+        _ORACLE_RUN[golden_dir] = (g, sc, oracle.evaluate_scene(sc, state, k=96, n_iter=19, sharpen=20.0, min_visible=1))
+    return _ORACLE_RUN[golden_dir]
+
+
 def _checksum(x):
     x = torch.as_tensor(x).double()
     return torch.stack([x.sum(1), (x * x).sum(1)], 1).numpy()
@@ -194,8 +205,7 @@ def _checksum(x):
 def test_oracle_whole_path_matches_reference_run(golden_dir):
     """The oracle against `SonataXAffinityTrainer.evaluate_scene` of the reference, executed unmodified in the build
     container (third-party operators stood in by definition stubs; see make_golden_scene.py)."""
-    g, sc, state = _golden_scene(golden_dir)
-    ref = oracle.evaluate_scene(sc, state, k=96, n_iter=19, sharpen=20.0, min_visible=1)
+    g, sc, ref = _oracle_run(golden_dir)
     assert list(ref["kept"]) == list(g["kept"])
     rows = g["rows"]
     # A4: gather + mean over views + KDTree fill -- same float32 operations in the same order
@@ -209,3 +219,61 @@ def test_oracle_whole_path_matches_reference_run(golden_dir):
     logits = torch.nn.functional.normalize(got, dim=-1) @ torch.nn.functional.normalize(torch.as_tensor(sc.text), dim=-1).t()
     sure = g["margin"] > 1e-4
     assert (logits.argmax(1).numpy()[sure] == g["labels"][sure]).all()
+
+
+def _xdecoder_golden(golden_dir):
+    import ast
+    g = np.load(os.path.join(golden_dir, "scene_xdecoder.npz"))
+    sc = synth.make_scene(**ast.literal_eval(str(g["scene_kwargs"])))
+    assert np.array_equal(sc.coords.astype(np.float32), g["coords"]), "synthetic scene generator drifted from the golden run"
+    W, H = sc.image_dim
+    masks, logits, embed = synth.make_mask_predictions(len(g["kept"]), int(g["n_queries"]), (H, W), sc.text, 512,
+                                                       int(g["mask_seed"]))
+    n, V = sc.n_points, len(g["kept"])
+    vis = g["mask_2ds"][:, 1].reshape(V, n).astype(bool)
+    pids = [np.nonzero(vis[v])[0] for v in range(V)]
+    cuts = np.cumsum([0] + [len(p) for p in pids])
+    rows = [g["x_labels"][cuts[v]:cuts[v + 1]].astype(np.int64) for v in range(V)]
+    cols = [g["y_labels"][cuts[v]:cuts[v + 1]].astype(np.int64) for v in range(V)]
+    return g, sc, masks, logits, embed, pids, rows, cols
+
+
+def test_oracle_consensus_lifting_matches_reference_run(golden_dir):
+    """A5 (+F3): the oracle against the reference's `lift_xdecoder_features`, executed unmodified in the build
+    container with the X-Decoder forward replaced by seeded head outputs (make_golden_scene.py:xdecoder_case)."""
+    g, sc, masks, logits, embed, pids, rows, cols = _xdecoder_golden(golden_dir)
+    Q = masks.shape[1]
+    vpf = []
+    for v in range(len(pids)):
+        _, _, idmap = oracle.mask_partition(masks[v], logits[v])
+        table = np.concatenate([embed[v], np.zeros((1, embed.shape[2]), np.float32)], 0)
+        vpf.append(table[idmap.numpy()[rows[v], cols[v]]])
+        assert (idmap.numpy() == Q).any() and (idmap.numpy() < Q).any()       # the case has holes to fill
+    got, _ = oracle.lift_consensus(sc.n_points, sc.coords.astype(np.float32), vpf, pids, sc.text, sc.logit_scale)
+    r = g["rows"]
+    assert np.abs(got[r].numpy() - g["lifted_rows"]).max() <= 1e-6
+    assert np.allclose(_checksum(got), g["lifted_checksum"], rtol=1e-6, atol=1e-6)
+
+
+def test_oracle_classification_and_metric_match_reference_validate(golden_dir):
+    """A12: oracle.classify + intersection_and_union against the reference's `validate()` run over two scenes
+    (tests/golden/validate_two_scenes.npz): predictions after the (y, z)-only KDTree fill of zero rows, per-scene
+    histograms, Base / Novel mIoU."""
+    g, sc, ref = _oracle_run(golden_dir)
+    gv = np.load(os.path.join(golden_dir, "validate_two_scenes.npz"))
+    feats = ref["scene_features"]
+    second = feats.clone()
+    second[torch.as_tensor(gv["zero_rows"]).long()] = 0.0
+    tgt = torch.as_tensor(sc.labels)
+    live = sc.labels != sc.ignore_label
+    sums = np.zeros((3, 20))
+    for k, f in enumerate((feats, second)):
+        pred, _ = oracle.classify(f, sc.text, sc.logit_scale, torch.as_tensor(g["coords"])[:, 1:4])
+        assert (pred.numpy()[live] == gv["pred"][k][live]).all(), f"scene {k}"
+        i_, u_, t_ = oracle.intersection_and_union(pred, tgt, 20, (sc.ignore_label,))
+        assert np.array_equal(np.asarray(i_), gv["inter"][k]) and np.array_equal(np.asarray(u_), gv["union"][k])
+        assert np.array_equal(np.asarray(t_), gv["target"][k])
+        sums += np.stack([np.asarray(i_), np.asarray(u_), np.asarray(t_)])
+    iou = sums[0].astype(np.float32) / (sums[1].astype(np.float32) + 1e-10)
+    assert abs(float(np.mean(iou[gv["base"]])) - float(gv["miou_base"])) < 1e-7
+    assert abs(float(np.mean(iou[gv["novel"]])) - float(gv["miou_novel"])) < 1e-7

@@ -643,3 +643,80 @@ def test_run_scene_matches_reference_run(gp, reference_scene):
     _check_against_reference_run(g, sc, feats)
     sure = (g["margin"] > 1e-4) & (sc.labels != sc.ignore_label)   # `pred` carries the ignore id where the target does
     assert (out["pred"].cpu().numpy()[sure] == g["labels"][sure]).all()
+
+
+def test_consensus_lifting_matches_reference_run(gp, golden_dir):
+    """A5 + F3 through the reference-facing call against the reference's own `lift_xdecoder_features` run
+    (tests/golden/scene_xdecoder.npz; X-Decoder forward replaced by seeded head outputs)."""
+    import ast
+    from geopurify_b200.affinity_module import SonataXAffinityTrainer
+    g = np.load(os.path.join(golden_dir, "scene_xdecoder.npz"))
+    sc = synth.make_scene(**ast.literal_eval(str(g["scene_kwargs"])))
+    assert np.array_equal(sc.coords.astype(np.float32), g["coords"])
+    W, H = sc.image_dim
+    masks, logits, embed = synth.make_mask_predictions(len(g["kept"]), int(g["n_queries"]), (H, W), sc.text, 512,
+                                                       int(g["mask_seed"]))
+    idmap, _ = gp.mask_partition(torch.as_tensor(masks).cuda(), torch.as_tensor(logits).cuda())
+    table = gp.mask_table(torch.as_tensor(embed).cuda())
+    batch_data = [None] * 20
+    batch_data[0] = torch.as_tensor(g["coords"]).float()
+    batch_data[12] = torch.as_tensor(g["x_labels"]).long()
+    batch_data[13] = torch.as_tensor(g["y_labels"]).long()
+    batch_data[14] = torch.as_tensor(g["mask_2ds"]).long()
+    model = SonataXAffinityTrainer(text_features=sc.text, logit_scale=sc.logit_scale,
+                                   mask_features=lambda bd: (idmap, table))
+    lifted, _, _ = model.lift_xdecoder_features(tuple(batch_data))
+    rows = torch.as_tensor(g["rows"]).long()
+    err = (lifted.cpu()[rows] - torch.as_tensor(g["lifted_rows"])).abs().max(1).values
+    assert int((err > 1e-5).sum()) == 0, f"{int((err > 1e-5).sum())} rows differ, max {err.max():.3e}"
+    x = lifted.double().cpu()
+    cs = torch.stack([x.sum(1), (x * x).sum(1)], 1).numpy()
+    assert np.allclose(cs, g["lifted_checksum"], rtol=1e-4, atol=1e-4)
+
+
+def test_validate_matches_reference_run(gp, golden_dir, reference_scene):
+    """A12 end to end: `validation.validate` over the two-scene loader of tests/golden/validate_two_scenes.npz against
+    the reference's own `run/validation.py:validate` (predictions after the zero-row fill, per-scene histograms, the
+    Base / Novel mIoU it returns)."""
+    from geopurify_b200 import validation
+    from geopurify_b200.affinity_module import SonataXAffinityTrainer
+    g, sc, student = reference_scene
+    gv = np.load(os.path.join(golden_dir, "validate_two_scenes.npz"))
+    maps = torch.stack([torch.as_tensor(sc.dense_map(v)) for v in g["kept"]]).cuda().contiguous()
+    batch_data = [None] * 20
+    batch_data[0] = torch.as_tensor(g["coords"]).float()
+    batch_data[1] = torch.as_tensor(g["voxel_coords"]).float()
+    batch_data[2] = torch.as_tensor(g["inds_reconstruct"]).long()
+    batch_data[3] = torch.as_tensor(sc.labels).long()
+    batch_data[12] = torch.as_tensor(g["x_labels"]).long()
+    batch_data[13] = torch.as_tensor(g["y_labels"]).long()
+    batch_data[14] = torch.as_tensor(g["mask_2ds"]).long()
+    batch_data[19] = torch.as_tensor(sc.gauss).float()
+    batch_data = tuple(batch_data)
+    model = SonataXAffinityTrainer(text_features=sc.text, logit_scale=sc.logit_scale, student=student,
+                                   view_features=lambda bd: maps)
+    first = model.evaluate_scene(batch_data)
+    second = dict(first)
+    second["scene_features"] = first["scene_features"].clone()
+    second["scene_features"][torch.as_tensor(gv["zero_rows"]).long().cuda()] = 0.0
+    results = [first, second]
+
+    class Replay:
+        calls = 0
+
+        def evaluate_scene(self, bd):
+            Replay.calls += 1
+            return results[Replay.calls - 1]
+
+    for k, res in enumerate(results):
+        pred = validation.classify_scene(res["scene_features"], res["text_features"], res["logit_scale"], batch_data[0])
+        want = gv["pred"][k].astype(np.int64)
+        live = sc.labels != sc.ignore_label            # the recorded predictions carry the ignore id on ignored targets
+        assert (pred.cpu().numpy()[live] == want[live]).all(), f"scene {k}"
+    (miou, macc, allacc), sums = validation.validate([batch_data, batch_data], Replay(), 20, [sc.ignore_label])
+    assert np.array_equal(sums[0], gv["inter"].sum(0)) and np.array_equal(sums[1], gv["union"].sum(0))
+    assert np.array_equal(sums[2], gv["target"].sum(0))
+    iou = sums[0].astype(np.float32) / (sums[1].astype(np.float32) + 1e-10)
+    assert abs(float(np.mean(iou[gv["base"]])) - float(gv["miou_base"])) < 1e-7
+    assert abs(float(np.mean(iou[gv["novel"]])) - float(gv["miou_novel"])) < 1e-7
+    assert abs(miou - float(np.mean(iou))) < 1e-7
