@@ -80,7 +80,9 @@ def scene_kwargs(args):
 
 def scene_sizes(args, rank):
     from geopurify_b200 import synth
-    rng = np.random.default_rng(5557 + 1000 * rank)
+    # weak scaling: every rank gets the SAME list of scene sizes (per-GPU work fixed as N grows); the scenes'
+    # contents are seeded per rank.  Rank-dependent sizes made the max-over-ranks time follow the unluckiest draw.
+    rng = np.random.default_rng(5557)
     if args.points:
         return [args.points] * args.pool
     # first scene of every rank is the headline ~150k-point shape; the rest follow the val size distribution
@@ -157,7 +159,14 @@ def cpu_sample_scene(args):
 def cpu_run(args, sc, state, repeats=1):
     """Times oracle.evaluate_scene (the CPU restatement of the reference path) on the host cores."""
     import torch
+    # all the host threads this process may use: torchrun exports OMP_NUM_THREADS=1 to every rank, which would time
+    # the CPU arm on one core.  Set before the oracle's OpenMP kNN library is loaded (it reads the variable then).
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    torch.set_num_threads(cores)
     from oracle import oracle
+    from sklearn.neighbors import KDTree  # noqa: F401  (first import costs seconds: keep it out of the timed region)
+    oracle.knn_c(np.arange(3 * 200, dtype=np.float32).reshape(200, 3), 4)   # loads the OpenMP kNN library
     stages = {}
     t0 = time.perf_counter()
     for _ in range(repeats):
