@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Summarise an ncu launch list (gpu__time_duration.sum CSV) and, optionally, a --set full .ncu-rep.
 
-    python profiles/summarize.py gpurun_out/launches.csv [gpurun_out/prof.ncu-rep] > profiles/rNN_x.txt
+    python profiles/summarize.py gpurun_out/launches.csv [gpurun_out/prof.ncu-rep ...] > profiles/rNN_x.txt
 """
 import collections
 import csv
@@ -46,5 +46,5 @@ def full(path):
 
 if __name__ == "__main__":
     launches(sys.argv[1])
-    if len(sys.argv) > 2:
-        full(sys.argv[2])
+    for rep in sys.argv[2:]:
+        full(rep)
