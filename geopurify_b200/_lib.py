@@ -58,6 +58,8 @@ _SIGS = {
     "gp_voxel_index_build": (c_int, [_P, c_int64, c_int, c_int, c_int, _P, _P, _P, c_size_t, _P]),
     "gp_kernel_map": (c_int, [_P, c_int64, c_int, c_int, c_int, _P, _P]),
     "gp_knn_grid": (c_int, [_P, c_int64, c_int, c_int, c_int, c_int, _P, _P, _P]),
+    "gp_knn_points_workspace_bytes": (c_size_t, [c_int64]),
+    "gp_knn_points": (c_int, [_P, c_int64, c_int, c_float, _P, _P, c_size_t, _P]),
     "gp_scatter_mean_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "gp_scatter_mean_prepare": (c_int, [_P, c_int64, c_int64, _P, c_size_t, _P]),
     "gp_scatter_mean": (c_int, [_P, c_int64, c_int, _P, c_int64, c_int64, _P, c_int64, c_int, _P]),

@@ -266,6 +266,19 @@ class VoxelIndex:
         return no, ns
 
 
+def knn_points(xyz_f32, k, min_cell=1e-3):
+    """F4: exact K nearest neighbours of raw float32 points, self excluded, ascending (float32 d2, index)
+    (faiss search on scene_coords, models/affinity_module.py:1159-1165).  Returns [n,k] int32."""
+    lib = L.load()
+    n = xyz_f32.shape[0]
+    out = torch.empty((n, k), dtype=torch.int32, device=_dev())
+    nb = lib.gp_knn_points_workspace_bytes(n)
+    ws = _ws(nb)
+    L.check(lib.gp_knn_points(L.ptr(xyz_f32), n, k, float(min_cell), L.ptr(out), L.ptr(ws), nb, L.stream()))
+    L.count(9)
+    return out
+
+
 class ScatterPlan:
     """CSR of points per destination row, reused for every scatter_mean with the same index."""
 

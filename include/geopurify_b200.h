@@ -187,6 +187,15 @@ int gp_kernel_map(const void* index_workspace, int64_t m, int ex, int ey, int ez
 int gp_knn_grid(const void* index_workspace, int64_t m, int ex, int ey, int ez, int K, int32_t* nbr_orig,
                 int32_t* nbr_sorted, gp_stream_t stream);
 
+/* ---- F4 (training-side sampling): exact K nearest neighbours on RAW float points, self excluded, ascending
+ * (d2, index) with d2 evaluated in float32 as ((dx*dx + dy*dy) + dz*dz), every operation rounded once
+ * (faiss IndexFlatL2 add/search on scene_coords at models/affinity_module.py:1159-1165, first column dropped).
+ *   xyz [n,3] float32;  nbr (out) [n,K] int32;  K <= 128, n >= K+1;  min_cell = lower bound of the grid cell edge, which is
+ *   otherwise chosen for about 32 points per cell at the bounding box's surface density */
+size_t gp_knn_points_workspace_bytes(int64_t n);
+int gp_knn_points(const float* xyz, int64_t n, int K, float min_cell, int32_t* nbr, void* workspace,
+                  size_t workspace_bytes, gp_stream_t stream);
+
 /* ---- A6: torch_scatter.scatter_mean (models/affinity_module.py:1524-1535), deterministic: float32 sum in
  * ascending point order, divided by the count.
  *   src  [n, src_stride] float32, D columns used;  p2v [n] int32 point -> destination row (already composed

@@ -394,6 +394,24 @@ def knn_c(voxel_coords, k):
 
 
 # ----------------------------------------------------------------------------- A10 / A11
+def knn_points(xyz, k, chunk=512):
+    """Training-side kNN on raw points (models/affinity_module.py:1159-1165): faiss IndexFlatL2 over float32
+    coordinates, K+1 results with the self column dropped.  Restated as the direct float32 evaluation
+    d2 = (dx*dx + dy*dy) + dz*dz (each numpy float32 operation rounds once), ascending (d2, index), self excluded."""
+    x = np.ascontiguousarray(xyz, dtype=np.float32)
+    n = x.shape[0]
+    out = np.empty((n, k), dtype=np.int64)
+    for s in range(0, n, chunk):
+        q = x[s:s + chunk]
+        dx = x[None, :, 0] - q[:, None, 0]
+        dy = x[None, :, 1] - q[:, None, 1]
+        dz = x[None, :, 2] - q[:, None, 2]
+        d2 = (dx * dx + dy * dy) + dz * dz
+        d2[np.arange(q.shape[0]), np.arange(s, s + q.shape[0])] = np.inf
+        out[s:s + chunk] = np.argsort(d2, axis=1, kind="stable")[:, :k]
+    return out
+
+
 def affinity_weights(embed, nbr_idx, sharpen=20.0):
     """cosine affinities + softmax(20 x) (models/affinity_module.py:1559-1572)."""
     e = torch.as_tensor(embed).float()

@@ -720,3 +720,32 @@ def test_validate_matches_reference_run(gp, golden_dir, reference_scene):
     assert abs(float(np.mean(iou[gv["base"]])) - float(gv["miou_base"])) < 1e-7
     assert abs(float(np.mean(iou[gv["novel"]])) - float(gv["miou_novel"])) < 1e-7
     assert abs(miou - float(np.mean(iou))) < 1e-7
+
+
+# ----------------------------------------------------------------------------- F4 kNN on raw points
+@pytest.mark.parametrize("n,k,kind", [(6000, 96, "surface"), (3000, 16, "volume"), (200, 96, "surface"),
+                                      (4000, 32, "lattice")])
+def test_knn_points_matches_oracle(gp, n, k, kind):
+    """Exact float32 kNN on raw points (training-side sampling) vs the brute-force oracle, order included."""
+    from oracle import oracle
+    rng = np.random.default_rng(n + k)
+    if kind == "surface":
+        xyz = synth.make_scene(n_points=n, n_views=1, image_dim=(32, 24), feat_dim=8, seed=3,
+                               room=(2.0, 1.6, 2.2), n_boxes=2).coords.astype(np.float32)
+    elif kind == "volume":
+        xyz = (rng.random((n, 3)) * np.array([3.0, 2.0, 1.0]) - 1.0).astype(np.float32)
+    else:   # points on a lattice: many exactly equal distances -> the (d2, index) tie rule decides
+        xyz = (rng.integers(0, 12, (n, 3)) * 0.05).astype(np.float32)
+        xyz = np.unique(xyz, axis=0)
+        xyz = xyz[rng.permutation(xyz.shape[0])]
+    want = oracle.knn_points(xyz, k)
+    got = gp.knn_points(torch.as_tensor(xyz).cuda(), k).cpu().numpy()
+    assert got.shape == want.shape
+    bad = int((got != want).any(1).sum())
+    assert bad == 0, f"{bad} of {xyz.shape[0]} rows differ"
+
+
+def test_knn_points_rejects_too_few_points(gp):
+    from geopurify_b200._lib import GeoPurifyError
+    with pytest.raises(GeoPurifyError):
+        gp.knn_points(torch.zeros((10, 3), device="cuda"), 16)
