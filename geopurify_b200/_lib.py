@@ -60,6 +60,9 @@ _SIGS = {
     "gp_knn_grid": (c_int, [_P, c_int64, c_int, c_int, c_int, c_int, _P, _P, _P]),
     "gp_knn_points_workspace_bytes": (c_size_t, [c_int64]),
     "gp_knn_points": (c_int, [_P, c_int64, c_int, c_float, _P, _P, c_size_t, _P]),
+    "gp_mine_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
+    "gp_mine_contrastive": (c_int, [_P, c_int64, c_int, c_int64, _P, c_int, _P, c_int, c_int, c_int, _P, _P, _P,
+                                    c_size_t, _P]),
     "gp_scatter_mean_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "gp_scatter_mean_prepare": (c_int, [_P, c_int64, c_int64, _P, c_size_t, _P]),
     "gp_scatter_mean": (c_int, [_P, c_int64, c_int, _P, c_int64, c_int64, _P, c_int64, c_int, _P]),

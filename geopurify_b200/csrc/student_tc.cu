@@ -18,6 +18,7 @@
 #include <cub/device/device_scan.cuh>
 #include "common.cuh"
 #include "tc.cuh"
+#include "topk.cuh"
 
 namespace {
 
@@ -982,4 +983,373 @@ extern "C" int gp_logits_argmax_tc(const float* feat, int64_t stride, int D, int
   // near ties, all-zero rows and NaNs: the fp32 kernel decides (and sets their zero flags)
   return gp_logits_fix_rows(feat, stride, D, rows, text, C, logit_scale, label, zero, flags, ws + L.off_simt,
                             L.simt_bytes, st);
+}
+
+// ------------------------------------------------------------------ F4: hybrid contrastive mining on the tensor cores
+// Replaces SonataXAffinityTrainer.sample_contrastive_pairs_hybrid (models/affinity_module.py:1099-1136) for a given
+// anchor set: cosine similarities of A anchors against all n points, positive = arg-max (anchor excluded), 48 "macro"
+// negatives = the smallest similarities (anchor and positive excluded), 15 "micro" negatives = the least similar of
+// the anchor's K spatial neighbours (positive excluded).  Ties: lowest index first.
+// S = Fn[n, D] x Fn[anchors]^T runs through gather_gemm_tc_kernel<512> unchanged: rows = points (identity gather),
+// the 512-anchor chunks play the role of the kernel offsets (tile.offset selects the chunk's weight image), the fp32
+// result is stored chunk-major [chunk][n][512]; the selection passes then read it with lane = anchor (coalesced).
+namespace {
+
+constexpr int MINE_SEG = 16;     // row segments per anchor in the partial selection
+constexpr int MINE_LMAX = 64;    // longest macro list (n_macro + 1 <= MINE_LMAX)
+
+// rows -> unit rows (F.normalize, eps 1e-12) -> bf16 hi/lo planes [n][2][kp]; one warp per row
+__global__ void __launch_bounds__(256) mine_normalize_split_kernel(const float* __restrict__ f, int64_t stride, int D,
+                                                                    int kp, int64_t n, __nv_bfloat16* __restrict__ planes) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (r >= n) return;
+  float ss = 0.f;
+  for (int c = lane; c < D; c += 32) {
+    const float v = f[r * stride + c];
+    ss = fmaf(v, v, ss);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  const float inv = 1.f / fmaxf(sqrtf(ss), 1e-12f);
+  for (int c = lane; c < kp; c += 32) {
+    const float v = c < D ? f[r * stride + c] * inv : 0.f;
+    __nv_bfloat16 hi, lo;
+    split_bf16(v, hi, lo);
+    planes[r * 2 * kp + c] = hi;
+    planes[r * 2 * kp + kp + c] = lo;
+  }
+}
+
+// anchor rows of the planes -> pre-tiled weight image [chunk][plane][kstep][512][16]
+__global__ void mine_anchor_weights_kernel(const __nv_bfloat16* __restrict__ planes, const int32_t* __restrict__ anchors,
+                                           int A, int chunks, int kp, __nv_bfloat16* __restrict__ out) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t total = (int64_t)chunks * 2 * kp * 512;
+  if (t >= total) return;
+  const int kk = (int)(t % BK);
+  const int a = (int)((t / BK) % 512);
+  const int ks = (int)((t / (BK * 512)) % (kp / BK));
+  const int plane = (int)((t / ((int64_t)BK * 512 * (kp / BK))) % 2);
+  const int chunk = (int)(t / ((int64_t)BK * 512 * (kp / BK) * 2));
+  const int ai = chunk * 512 + a;
+  __nv_bfloat16 v = __float2bfloat16_rn(0.f);
+  if (ai < A) v = planes[(int64_t)anchors[ai] * 2 * kp + plane * kp + ks * BK + kk];
+  out[t] = v;
+}
+
+__global__ void mine_tiles_kernel(int64_t n, int chunks, int64_t n_pad, TileInfo* __restrict__ tiles) {
+  const int rt = (int)((n + TM - 1) / TM);
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= rt * chunks) return;
+  const int chunk = t / rt, r = t - chunk * rt;
+  TileInfo ti;
+  ti.offset = chunk;
+  ti.p0 = r * TM;
+  ti.nrows = (int)min((int64_t)TM, n - (int64_t)r * TM);
+  ti.c_row0 = (int)((int64_t)chunk * n_pad + (int64_t)r * TM);
+  tiles[t] = ti;
+}
+
+// (value, index) ascending with lowest index first on ties
+__device__ __forceinline__ bool mine_less(float v, int i, float w, int j) { return v < w || (v == w && i < j); }
+
+// Partial selection: a CTA owns 64 anchors x one row segment.  Row blocks of 32 x 64 similarities are staged in shared
+// memory (coalesced 256-byte rows), then every warp serves 8 of the anchors with lane = row: one compare against the
+// anchor's current threshold per element, and the rare survivors are inserted WARP-COOPERATIVELY into the anchor's list
+// of the 64 smallest keys (2 per lane, registers; key = orderable float bits << 32 | row) by replacing its maximum.
+__device__ __forceinline__ unsigned mine_f2ord(float f) {
+  const unsigned u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float mine_ord2f(unsigned u) {
+  return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
+__global__ void __launch_bounds__(256) mine_partial_kernel(const float* __restrict__ S, int64_t n, int64_t n_pad, int A,
+                                                            const int32_t* __restrict__ anchors, int L,
+                                                            float* __restrict__ pbest_v, int32_t* __restrict__ pbest_i,
+                                                            float* __restrict__ plist_v, int32_t* __restrict__ plist_i) {
+  __shared__ float tile[32][65];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int a0 = blockIdx.x * 64;  // 64 consecutive anchors: one 512-anchor chunk, 256 contiguous bytes per row
+  const int seg = blockIdx.y;
+  const int chunk = a0 >> 9, col0 = a0 & 511;
+  const float* base = S + ((int64_t)chunk * n_pad) * 512 + col0;
+  const int64_t rows_per = (n + MINE_SEG - 1) / MINE_SEG;
+  const int64_t r0 = seg * rows_per, r1 = min(n, r0 + rows_per);
+  u64 key[8][2], thr[8];
+  int self[8];
+  float best[8];
+  int besti[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int a = a0 + warp * 8 + k;
+    self[k] = a < A ? __ldg(anchors + a) : -1;
+    key[k][0] = ~0ull - (u64)(lane);        // 64 distinct "empty" keys; the largest is replaced first
+    key[k][1] = ~0ull - (u64)(lane + 32);
+    thr[k] = ~0ull;
+    best[k] = -INFINITY;
+    besti[k] = -1;
+  }
+  for (int64_t rb = r0; rb < r1; rb += 32) {
+    __syncthreads();
+    {  // 32 rows x 64 anchors, 16 threads x float4 per row, 16 rows per pass
+      const int c4 = (threadIdx.x & 15) * 4;
+#pragma unroll
+      for (int pass = 0; pass < 2; ++pass) {
+        const int rr = pass * 16 + (threadIdx.x >> 4);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rb + rr < r1) v = __ldg((const float4*)(base + (rb + rr) * 512 + c4));
+        tile[rr][c4] = v.x;
+        tile[rr][c4 + 1] = v.y;
+        tile[rr][c4 + 2] = v.z;
+        tile[rr][c4 + 3] = v.w;
+      }
+    }
+    __syncthreads();
+    const int64_t r = rb + lane;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float v = tile[lane][warp * 8 + k];
+      const bool ok = r < r1 && (int)r != self[k];
+      if (ok && (v > best[k] || besti[k] < 0)) {  // ascending rows inside a lane: strict > keeps the lowest row
+        best[k] = v;
+        besti[k] = (int)r;
+      }
+      const u64 cand = ((u64)mine_f2ord(v) << 32) | (u64)(unsigned)r;
+      unsigned pend = __ballot_sync(0xffffffffu, ok && cand < thr[k]);
+      while (pend) {
+        const int src = __ffs(pend) - 1;
+        const u64 ck = __shfl_sync(0xffffffffu, cand, src);
+        pend &= pend - 1;
+        if (ck >= thr[k]) continue;  // an earlier insertion lowered the threshold below this candidate
+        // replace the list's maximum, then find the new maximum (= threshold)
+        u64 lm = key[k][0] > key[k][1] ? key[k][0] : key[k][1];
+        u64 wm = lm;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const u64 other = __shfl_xor_sync(0xffffffffu, wm, o);
+          wm = other > wm ? other : wm;
+        }
+        if (key[k][0] == wm) key[k][0] = ck;
+        else if (key[k][1] == wm) key[k][1] = ck;
+        lm = key[k][0] > key[k][1] ? key[k][0] : key[k][1];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const u64 other = __shfl_xor_sync(0xffffffffu, lm, o);
+          lm = other > lm ? other : lm;
+        }
+        thr[k] = lm;
+      }
+    }
+  }
+  // ---- write the segment's results: arg-max and the L smallest in ascending (value, row) order
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int a = a0 + warp * 8 + k;
+    float bv = best[k];
+    int bi = besti[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (oi >= 0 && (bi < 0 || ov > bv || (ov == bv && oi < bi))) {
+        bv = ov;
+        bi = oi;
+      }
+    }
+    u64 srt[4] = {key[k][0], key[k][1], ~0ull, ~0ull};
+    bitonic_sort128(srt, lane);
+    if (a < A) {
+      if (lane == 0) {
+        pbest_v[(int64_t)seg * A + a] = bv;
+        pbest_i[(int64_t)seg * A + a] = bi;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e = lane * 4 + j;
+        if (e < L) {
+          const bool real = (srt[j] >> 32) != 0xffffffffull;  // "empty" keys have all-ones upper words
+          plist_v[((int64_t)seg * L + e) * A + a] = real ? mine_ord2f((unsigned)(srt[j] >> 32)) : INFINITY;
+          plist_i[((int64_t)seg * L + e) * A + a] = real ? (int)(srt[j] & 0xffffffffu) : -1;
+        }
+      }
+    }
+  }
+}
+
+// thread = anchor: merge the segments, then pick the micro negatives among the spatial neighbours
+__global__ void mine_merge_kernel(const float* __restrict__ S, int64_t n_pad, int A, const int32_t* __restrict__ anchors,
+                                  const float* __restrict__ pbest_v, const int32_t* __restrict__ pbest_i,
+                                  const float* __restrict__ plist_v, const int32_t* __restrict__ plist_i, int L,
+                                  const int32_t* __restrict__ nbr, int K, int n_macro, int n_micro,
+                                  int32_t* __restrict__ positive, int32_t* __restrict__ negatives) {
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= A) return;
+  float best = -INFINITY;
+  int pos = -1;
+  for (int s = 0; s < MINE_SEG; ++s) {  // ascending segments = ascending rows: strict > keeps the lowest index
+    const float v = pbest_v[(int64_t)s * A + a];
+    const int i = pbest_i[(int64_t)s * A + a];
+    if (i >= 0 && (pos < 0 || v > best)) {
+      best = v;
+      pos = i;
+    }
+  }
+  positive[a] = pos;
+  int32_t* neg = negatives + (int64_t)a * (n_macro + n_micro);
+  int head[MINE_SEG];
+  for (int s = 0; s < MINE_SEG; ++s) head[s] = 0;
+  for (int j = 0; j < n_macro; ++j) {
+    int bs = -1, bi = -1;
+    float bv = INFINITY;
+    for (int s = 0; s < MINE_SEG; ++s) {
+      while (head[s] < L && plist_i[((int64_t)s * L + head[s]) * A + a] == pos) ++head[s];  // the positive is excluded
+      if (head[s] >= L) continue;
+      const int i = plist_i[((int64_t)s * L + head[s]) * A + a];
+      if (i < 0) continue;
+      const float v = plist_v[((int64_t)s * L + head[s]) * A + a];
+      if (bs < 0 || mine_less(v, i, bv, bi)) {
+        bs = s;
+        bv = v;
+        bi = i;
+      }
+    }
+    neg[j] = bi;
+    if (bs >= 0) ++head[bs];
+  }
+  // micro negatives: the n_micro smallest similarities among the K spatial neighbours, (value, list position) order
+  const int chunk = a >> 9, col = a & 511;
+  const float* base = S + ((int64_t)chunk * n_pad) * 512 + col;
+  const int32_t* nb = nbr + (int64_t)anchors[a] * K;
+  float mv[32];
+  int mk[32];
+  int cnt = 0;
+  for (int k = 0; k < K; ++k) {
+    const int p = nb[k];
+    const float v = p == pos ? INFINITY : __ldg(base + (int64_t)p * 512);
+    if (cnt < n_micro || mine_less(v, k, mv[cnt - 1], mk[cnt - 1])) {
+      int q = cnt < n_micro ? cnt : n_micro - 1;
+      while (q > 0 && mine_less(v, k, mv[q - 1], mk[q - 1])) {
+        mv[q] = mv[q - 1];
+        mk[q] = mk[q - 1];
+        --q;
+      }
+      mv[q] = v;
+      mk[q] = k;
+      if (cnt < n_micro) ++cnt;
+    }
+  }
+  for (int j = 0; j < n_micro; ++j) neg[n_macro + j] = j < cnt ? nb[mk[j]] : -1;
+}
+
+struct MineLayout {
+  int kp, chunks, L;
+  int64_t n_pad, ntiles;
+  size_t off_planes, off_w, off_tiles, off_S, off_pbv, off_pbi, off_plv, off_pli, bytes;
+};
+
+bool mine_layout(int64_t n, int D, int A, int n_macro, MineLayout& M) {
+  if (n < 1 || D < 1 || A < 1 || n >= (1ll << 31) / 8) return false;
+  M.kp = (D + BK - 1) / BK * BK;
+  M.chunks = (A + 511) / 512;
+  M.L = n_macro + 1;
+  M.n_pad = (n + TM - 1) / TM * TM;
+  M.ntiles = (M.n_pad / TM) * M.chunks;
+  if (M.n_pad * M.chunks >= (1ll << 31)) return false;  // TileInfo.c_row0 is an int
+  size_t off = 0;
+  auto take = [&](size_t b) {
+    size_t o = off;
+    off += gp_align_up(b, 1024);
+    return o;
+  };
+  M.off_planes = take(sizeof(__nv_bfloat16) * 2 * (size_t)n * M.kp);
+  M.off_w = take(sizeof(__nv_bfloat16) * 2 * (size_t)M.chunks * 512 * M.kp);
+  M.off_tiles = take(sizeof(TileInfo) * (size_t)M.ntiles);
+  M.off_S = take(sizeof(float) * (size_t)M.chunks * M.n_pad * 512);
+  M.off_pbv = take(sizeof(float) * (size_t)MINE_SEG * A);
+  M.off_pbi = take(sizeof(int32_t) * (size_t)MINE_SEG * A);
+  M.off_plv = take(sizeof(float) * (size_t)MINE_SEG * M.L * A);
+  M.off_pli = take(sizeof(int32_t) * (size_t)MINE_SEG * M.L * A);
+  M.bytes = off;
+  return true;
+}
+
+}  // namespace
+
+extern "C" size_t gp_mine_workspace_bytes(int64_t n, int D, int A, int n_macro) {
+  MineLayout M;
+  if (!mine_layout(n, D, A, n_macro, M)) return 0;
+  return M.bytes;
+}
+
+extern "C" int gp_mine_contrastive(const float* feat, int64_t stride, int D, int64_t n, const int32_t* anchors, int A,
+                                   const int32_t* nbr, int K, int n_macro, int n_micro, int32_t* positive,
+                                   int32_t* negatives, void* workspace, size_t workspace_bytes, gp_stream_t stream) {
+  GP_CHECK_ARG(feat && anchors && nbr && positive && negatives, "gp_mine_contrastive: null argument");
+  GP_CHECK_ARG(n_macro >= 1 && n_macro + 1 <= MINE_LMAX, "gp_mine_contrastive: n_macro=%d outside [1,%d]", n_macro,
+               MINE_LMAX - 1);
+  GP_CHECK_ARG(n_micro >= 0 && n_micro <= 32 && n_micro <= K, "gp_mine_contrastive: n_micro=%d outside [0,min(32,K)]",
+               n_micro);
+  GP_CHECK_ARG(n >= (int64_t)n_macro + 2, "gp_mine_contrastive: needs n >= n_macro + 2 points");
+  GP_CHECK_ARG(stride >= D, "gp_mine_contrastive: stride < D");
+  MineLayout M;
+  GP_CHECK_ARG(mine_layout(n, D, A, n_macro, M), "gp_mine_contrastive: bad sizes (n=%lld, D=%d, A=%d)", (long long)n, D, A);
+  GP_CHECK_ARG(((uintptr_t)workspace % 256) == 0, "gp_mine_contrastive: workspace must be 256-byte aligned");
+  if (workspace_bytes < M.bytes) {
+    gp_set_error("gp_mine_contrastive: workspace %zu < %zu", workspace_bytes, M.bytes);
+    return GP_ERR_WORKSPACE;
+  }
+  GP_CHECK_ARG(encode_tiled_fn() != nullptr, "gp_mine_contrastive: cuTensorMapEncodeTiled unavailable");
+  cudaStream_t st = (cudaStream_t)stream;
+  static int sm_count = 0;
+  if (!sm_count) {
+    int dev = 0;
+    GP_CUDA(cudaGetDevice(&dev));
+    GP_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+  }
+  char* ws = (char*)workspace;
+  __nv_bfloat16* planes = (__nv_bfloat16*)(ws + M.off_planes);
+  __nv_bfloat16* wimg = (__nv_bfloat16*)(ws + M.off_w);
+  TileInfo* tiles = (TileInfo*)(ws + M.off_tiles);
+  float* S = (float*)(ws + M.off_S);
+  mine_normalize_split_kernel<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(feat, stride, D, M.kp, n, planes);
+  GP_LAUNCH_CHECK();
+  {
+    const int64_t tot = (int64_t)M.chunks * 2 * M.kp * 512;
+    mine_anchor_weights_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(planes, anchors, A, M.chunks, M.kp, wimg);
+    GP_LAUNCH_CHECK();
+  }
+  mine_tiles_kernel<<<(unsigned)((M.ntiles + 255) / 256), 256, 0, st>>>(n, M.chunks, M.n_pad, tiles);
+  GP_LAUNCH_CHECK();
+  CUtensorMap map;
+  GP_CHECK_ARG(make_weight_map(&map, wimg, (int64_t)M.chunks * 2 * 512 * (M.kp / BK), 256 / (PAIR ? 2 : 1)),
+               "gp_mine_contrastive: cuTensorMapEncodeTiled failed");
+  GemmParams P = {};
+  P.a = planes;
+  P.lda = 2 * (int64_t)M.kp;
+  P.kp = M.kp;
+  P.pair_in = nullptr;
+  P.tiles = tiles;
+  P.ntiles_dev = nullptr;
+  P.ntiles_host = (int)M.ntiles;
+  P.m_rows = n;
+  P.cout_total = 512;
+  P.c = S;
+  P.ldc = 512;
+  int grid = P.ntiles_host < sm_count ? P.ntiles_host : sm_count;
+  int rc = launch_gemm<512>(map, P, grid, st);
+  if (rc) return rc;
+  float* pbv = (float*)(ws + M.off_pbv);
+  int32_t* pbi = (int32_t*)(ws + M.off_pbi);
+  float* plv = (float*)(ws + M.off_plv);
+  int32_t* pli = (int32_t*)(ws + M.off_pli);
+  dim3 pg((unsigned)((A + 63) / 64), MINE_SEG);
+  mine_partial_kernel<<<pg, 256, 0, st>>>(S, n, M.n_pad, A, anchors, M.L, pbv, pbi, plv, pli);
+  GP_LAUNCH_CHECK();
+  mine_merge_kernel<<<(unsigned)((A + 127) / 128), 128, 0, st>>>(S, M.n_pad, A, anchors, pbv, pbi, plv, pli, M.L, nbr, K,
+                                                               n_macro, n_micro, positive, negatives);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
 }

@@ -279,6 +279,24 @@ def knn_points(xyz_f32, k, min_cell=1e-3):
     return out
 
 
+def mine_contrastive(feat, anchors_i32, nbr_i32, n_macro=48, n_micro=15):
+    """F4: positives and hybrid negatives of `sample_contrastive_pairs_hybrid` (models/affinity_module.py:1099-1136)
+    for the given anchors.  Returns (positive [A] int32, negatives [A, n_macro + n_micro] int32)."""
+    lib = L.load()
+    n, d = feat.shape
+    a, k = anchors_i32.shape[0], nbr_i32.shape[1]
+    pos = torch.empty((a,), dtype=torch.int32, device=_dev())
+    neg = torch.empty((a, n_macro + n_micro), dtype=torch.int32, device=_dev())
+    nb = lib.gp_mine_workspace_bytes(n, d, a, n_macro)
+    if nb == 0:
+        raise L.GeoPurifyError(f"gp_mine_workspace_bytes: bad sizes n={n} D={d} A={a}")
+    ws = _ws(nb)
+    L.check(lib.gp_mine_contrastive(L.ptr(feat), feat.stride(0), d, n, L.ptr(anchors_i32), a, L.ptr(nbr_i32), k,
+                                    n_macro, n_micro, L.ptr(pos), L.ptr(neg), L.ptr(ws), nb, L.stream()))
+    L.count(6)
+    return pos, neg
+
+
 class ScatterPlan:
     """CSR of points per destination row, reused for every scatter_mean with the same index."""
 

@@ -196,6 +196,20 @@ size_t gp_knn_points_workspace_bytes(int64_t n);
 int gp_knn_points(const float* xyz, int64_t n, int K, float min_cell, int32_t* nbr, void* workspace,
                   size_t workspace_bytes, gp_stream_t stream);
 
+/* ---- F4 (training-side sampling): hybrid contrastive mining for a given anchor set
+ * (SonataXAffinityTrainer.sample_contrastive_pairs_hybrid, models/affinity_module.py:1099-1136, after its randperm).
+ *   feat      [n, stride] float32, D columns used (the 3-D teacher features); rows are L2-normalised internally
+ *   anchors   [A] int32 distinct point indices;  nbr [n,K] int32 spatial neighbours (gp_knn_points)
+ *   positive  (out) [A] int32   arg-max cosine similarity over all points except the anchor
+ *   negatives (out) [A, n_macro + n_micro] int32: the n_macro least similar points (anchor and positive excluded,
+ *             ascending similarity) followed by the n_micro least similar of the anchor's K neighbours (positive
+ *             excluded).  Ties: lowest index (macro) / earliest list position (micro) first.
+ * Similarities are an fp32-faithful tcgen05 GEMM (bf16 hi/lo split, error <= 2^-15). n_macro <= 63, n_micro <= 32. */
+size_t gp_mine_workspace_bytes(int64_t n, int D, int A, int n_macro);
+int gp_mine_contrastive(const float* feat, int64_t stride, int D, int64_t n, const int32_t* anchors, int A,
+                        const int32_t* nbr, int K, int n_macro, int n_micro, int32_t* positive, int32_t* negatives,
+                        void* workspace, size_t workspace_bytes, gp_stream_t stream);
+
 /* ---- A6: torch_scatter.scatter_mean (models/affinity_module.py:1524-1535), deterministic: float32 sum in
  * ascending point order, divided by the count.
  *   src  [n, src_stride] float32, D columns used;  p2v [n] int32 point -> destination row (already composed

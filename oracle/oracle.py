@@ -412,6 +412,29 @@ def knn_points(xyz, k, chunk=512):
     return out
 
 
+def mine_contrastive(feat, anchor_indices, neighbor_indices, n_neg=63, n_macro=48):
+    """`sample_contrastive_pairs_hybrid` after its randperm (models/affinity_module.py:1112-1136), same torch calls.
+    Returns (positive [A], negatives [A, n_neg], sim [A, N] with the anchor / positive entries at +inf)."""
+    f = torch.as_tensor(feat).float()
+    anchor_indices = torch.as_tensor(anchor_indices).long()
+    neighbor_indices = torch.as_tensor(neighbor_indices).long()
+    num_points = f.shape[0]
+    sim = torch.einsum('ad,pd->ap', F.normalize(f[anchor_indices], p=2, dim=1), F.normalize(f, p=2, dim=1))   # :1113
+    sim_pos = sim.clone()
+    sim_pos.scatter_(1, anchor_indices.unsqueeze(1), float('-inf'))                                          # :1117
+    positive = torch.argmax(sim_pos, dim=1)                                                                   # :1118
+    n_micro = n_neg - n_macro
+    ar = torch.arange(num_points)
+    exclude = (ar.unsqueeze(0) == anchor_indices.unsqueeze(1)) | (ar.unsqueeze(0) == positive.unsqueeze(1))   # :1124
+    sim[exclude] = float('inf')                                                                               # :1126
+    _, macro = torch.topk(sim, k=n_macro, largest=False, dim=1)                                               # :1127
+    nb = neighbor_indices[anchor_indices]                                                                     # :1129
+    local = torch.gather(sim, 1, nb)                                                                          # :1130
+    _, hardest = torch.topk(local, k=n_micro, largest=False, dim=1)                                           # :1131
+    micro = torch.gather(nb, 1, hardest)                                                                      # :1132
+    return positive, torch.cat([macro, micro], dim=1), sim
+
+
 def affinity_weights(embed, nbr_idx, sharpen=20.0):
     """cosine affinities + softmax(20 x) (models/affinity_module.py:1559-1572)."""
     e = torch.as_tensor(embed).float()

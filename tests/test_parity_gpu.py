@@ -749,3 +749,53 @@ def test_knn_points_rejects_too_few_points(gp):
     from geopurify_b200._lib import GeoPurifyError
     with pytest.raises(GeoPurifyError):
         gp.knn_points(torch.zeros((10, 3), device="cuda"), 16)
+
+
+# ----------------------------------------------------------------------------- F4 contrastive mining
+@pytest.mark.parametrize("n,d,a", [(3000, 64, 1000), (5000, 1232, 700), (700, 48, 233)])
+def test_mine_contrastive_matches_oracle(gp, n, d, a):
+    """Positives / macro / micro negatives of the hybrid sampler for a given anchor set.  Index equality is required
+    wherever the decision margin exceeds the tensor-core path's 1e-5 similarity tolerance; everywhere the chosen
+    entries must be as good as the oracle's within that tolerance."""
+    from oracle import oracle
+    rng = np.random.default_rng(n + d)
+    xyz = (rng.random((n, 3)) * np.array([4.0, 3.0, 2.5])).astype(np.float32)
+    cls = rng.integers(0, 12, n)
+    proto = rng.standard_normal((12, d)).astype(np.float32)
+    feat = (proto[cls] + 0.7 * rng.standard_normal((n, d))).astype(np.float32) * rng.uniform(0.5, 3.0, (n, 1)).astype(np.float32)
+    anchors = rng.permutation(n)[:a].astype(np.int32)
+    K, n_macro, n_micro = 96, 48, 15
+    nbr = oracle.knn_points(xyz, K)
+    want_pos, want_neg, sim = oracle.mine_contrastive(feat, anchors, nbr, n_macro + n_micro, n_macro)
+    pos, neg = gp.mine_contrastive(torch.as_tensor(feat).cuda(), torch.as_tensor(anchors).cuda(),
+                                   torch.as_tensor(nbr.astype(np.int32)).cuda(), n_macro, n_micro)
+    pos, neg = pos.cpu().long(), neg.cpu().long()
+    tol = 1e-5
+    rows = torch.arange(a)
+    # positives: sim here has +inf on the anchor and on the ORACLE's positive -> rebuild the plain similarities
+    plain = torch.einsum('ad,pd->ap', torch.nn.functional.normalize(torch.as_tensor(feat)[anchors.astype(np.int64)], dim=1),
+                         torch.nn.functional.normalize(torch.as_tensor(feat), dim=1))
+    masked = plain.clone()
+    masked[rows, torch.as_tensor(anchors).long()] = -np.inf
+    top2 = masked.topk(2, dim=1).values
+    assert (pos != torch.as_tensor(anchors).long()).all()
+    assert (masked[rows, pos] >= top2[:, 0] - tol).all()
+    sure = (top2[:, 0] - top2[:, 1]) > 10 * tol
+    assert (pos[sure] == want_pos[sure]).all()
+    # macro negatives: 48 distinct points, none the anchor or the positive, all within tol of the 48 smallest
+    ok_rows = pos == want_pos
+    s_sorted = sim.sort(dim=1).values
+    for r in torch.nonzero(ok_rows).flatten()[:400].tolist():
+        m = neg[r, :n_macro]
+        assert len(set(m.tolist())) == n_macro and int(anchors[r]) not in m.tolist() and int(pos[r]) not in m.tolist()
+        assert (sim[r, m] <= s_sorted[r, n_macro - 1] + tol).all()
+        if s_sorted[r, n_macro] - s_sorted[r, n_macro - 1] > 10 * tol:
+            assert set(m.tolist()) == set(want_neg[r, :n_macro].tolist())
+        # micro negatives: among the anchor's spatial neighbours, within tol of the 15 smallest local similarities
+        nb = torch.as_tensor(nbr[anchors[r]])
+        mi = neg[r, n_macro:]
+        assert set(mi.tolist()) <= set(nb.tolist()) and len(set(mi.tolist())) == n_micro
+        loc = sim[r, nb].sort().values
+        assert (sim[r, mi] <= loc[n_micro - 1] + tol).all()
+        if loc[n_micro] - loc[n_micro - 1] > 10 * tol:
+            assert set(mi.tolist()) == set(want_neg[r, n_macro:].tolist())
