@@ -336,3 +336,12 @@ def make_mask_predictions(n_views, n_queries, image_hw, text, feat_dim=512, seed
             logits[v, q] = row.astype(np.float32)
             embed[v, q] = (text[cls].astype(np.float64) + rng.normal(0.0, 0.05, feat_dim)).astype(np.float32)
     return masks, logits, embed
+
+
+def make_mining_inputs(n=1500, d=64, seed=11, n_clusters=10):
+    """Seeded inputs for the training-side sampling kernels (F4): random points in a room and clustered features."""
+    rng = np.random.default_rng(seed)
+    xyz = (rng.random((n, 3)) * np.array([4.0, 3.0, 2.5])).astype(np.float32)
+    proto = rng.standard_normal((n_clusters, d)).astype(np.float32)
+    feat = (proto[rng.integers(0, n_clusters, n)] + 0.7 * rng.standard_normal((n, d))).astype(np.float32)
+    return xyz, feat

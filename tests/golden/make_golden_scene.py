@@ -167,6 +167,7 @@ def main():
         stubbed=np.array(sorted(set(s.split(".")[0] for s in ref_stubs.stubbed))))
     validate_case(sc, t, batch_data, out)
     xdecoder_case(sc, t, batch_data, kept)
+    mining_case(t)
     print("kept views", kept, "points", feats.shape[0], "voxels", scene_vox.shape[0],
           "stubbed:", sorted(set(s.split(".")[0] for s in ref_stubs.stubbed)))
     print("feature range", float(feats.min()), float(feats.max()), "min margin", float((top2[:, 0] - top2[:, 1]).min()))
@@ -269,6 +270,30 @@ def xdecoder_case(sc, t, batch_data, kept):
         rows=rows, lifted_rows=lifted[rows].numpy(), lifted_checksum=checksum(lifted),
         text_normalised_checksum=checksum(text_n))
     print("xdecoder lifting:", tuple(lifted.shape), "all-zero rows", zero_rows, "logit_scale", float(scale))
+
+
+MINE = dict(n=1500, d=64, seed=11, torch_seed=5557)
+
+
+def mining_inputs():
+    """Seeded inputs of the mining case (tests rebuild them the same way): points, clustered features, their kNN."""
+    from oracle import oracle
+    xyz, feat = synth.make_mining_inputs(MINE["n"], MINE["d"], MINE["seed"])
+    return xyz, feat, oracle.knn_points(xyz, 96)
+
+
+def mining_case(t):
+    """F4: the reference's `sample_contrastive_pairs_hybrid` (models/affinity_module.py:1099-1136) executed unmodified;
+    its `torch.randperm` anchors are stored with the outputs."""
+    xyz, feat, nbr = mining_inputs()
+    t.num_anchors_per_scene, t.num_negatives_per_anchor = 4096, 63
+    torch.manual_seed(MINE["torch_seed"])
+    with torch.no_grad():
+        anchor, pos, neg = t.sample_contrastive_pairs_hybrid(torch.from_numpy(feat), torch.from_numpy(nbr))
+    np.savez_compressed(os.path.join(HERE, "mining_hybrid.npz"), params=np.array(repr(MINE)),
+                        feat_checksum=np.float64(feat.astype(np.float64).sum()), anchors=anchor.numpy().astype(np.int32),
+                        positive=pos.numpy().astype(np.int32), negatives=neg.numpy().astype(np.int32))
+    print("mining:", tuple(anchor.shape), tuple(pos.shape), tuple(neg.shape))
 
 
 if __name__ == "__main__":

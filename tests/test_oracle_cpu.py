@@ -277,3 +277,17 @@ def test_oracle_classification_and_metric_match_reference_validate(golden_dir):
     iou = sums[0].astype(np.float32) / (sums[1].astype(np.float32) + 1e-10)
     assert abs(float(np.mean(iou[gv["base"]])) - float(gv["miou_base"])) < 1e-7
     assert abs(float(np.mean(iou[gv["novel"]])) - float(gv["miou_novel"])) < 1e-7
+
+
+def test_oracle_mining_matches_reference_run(golden_dir):
+    """F4: oracle.mine_contrastive against the reference's `sample_contrastive_pairs_hybrid` run
+    (tests/golden/mining_hybrid.npz, anchors = the reference's own randperm)."""
+    import ast
+    g = np.load(os.path.join(golden_dir, "mining_hybrid.npz"))
+    prm = ast.literal_eval(str(g["params"]))
+    xyz, feat = synth.make_mining_inputs(prm["n"], prm["d"], prm["seed"])
+    assert abs(float(feat.astype(np.float64).sum()) - float(g["feat_checksum"])) < 1e-9
+    nbr = oracle.knn_points(xyz, 96)
+    pos, neg, _ = oracle.mine_contrastive(feat, g["anchors"], nbr, 63, 48)
+    assert np.array_equal(pos.numpy(), g["positive"])
+    assert np.array_equal(neg.numpy(), g["negatives"])

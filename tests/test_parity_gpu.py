@@ -799,3 +799,37 @@ def test_mine_contrastive_matches_oracle(gp, n, d, a):
         assert (sim[r, mi] <= loc[n_micro - 1] + tol).all()
         if loc[n_micro] - loc[n_micro - 1] > 10 * tol:
             assert set(mi.tolist()) == set(want_neg[r, n_macro:].tolist())
+
+
+def test_mine_contrastive_matches_reference_run(gp, golden_dir):
+    """F4 against the reference's own `sample_contrastive_pairs_hybrid` output for the reference's own anchors."""
+    import ast
+    from oracle import oracle
+    g = np.load(os.path.join(golden_dir, "mining_hybrid.npz"))
+    prm = ast.literal_eval(str(g["params"]))
+    xyz, feat = synth.make_mining_inputs(prm["n"], prm["d"], prm["seed"])
+    nbr = gp.knn_points(torch.as_tensor(xyz).cuda(), 96)
+    assert np.array_equal(nbr.cpu().numpy(), oracle.knn_points(xyz, 96))
+    pos, neg = gp.mine_contrastive(torch.as_tensor(feat).cuda(), torch.as_tensor(g["anchors"]).cuda(), nbr, 48, 15)
+    pos, neg = pos.cpu().numpy(), neg.cpu().numpy()
+    # similarities in float64 decide which rows are safely away from ties
+    f = feat.astype(np.float64)
+    f /= np.linalg.norm(f, axis=1, keepdims=True)
+    sim = f[g["anchors"]] @ f.T
+    a = len(g["anchors"])
+    sim[np.arange(a), g["anchors"]] = -np.inf
+    top2 = -np.sort(-sim, axis=1)[:, :2]
+    sure = (top2[:, 0] - top2[:, 1]) > 1e-4
+    assert sure.mean() > 0.9 and (pos[sure] == g["positive"][sure]).all()
+    sim[np.arange(a), g["anchors"]] = np.inf
+    sim[np.arange(a), g["positive"]] = np.inf
+    srt = np.sort(sim, axis=1)
+    checked = 0
+    for r in np.nonzero(sure)[0]:
+        if srt[r, 48] - srt[r, 47] > 1e-4:
+            assert set(neg[r, :48].tolist()) == set(g["negatives"][r, :48].tolist())
+            checked += 1
+        loc = np.sort(sim[r, nbr[g["anchors"][r]].cpu().numpy()])
+        if loc[15] - loc[14] > 1e-4:
+            assert set(neg[r, 48:].tolist()) == set(g["negatives"][r, 48:].tolist())
+    assert checked > a // 2
