@@ -456,15 +456,25 @@ __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bflo
 
 __global__ void tc_split_input_kernel(const float* __restrict__ x, int64_t stride, int cin, int kp, int64_t m,
                                       __nv_bfloat16* __restrict__ out) {
+  // four columns per thread: one 16-byte load, two 8-byte stores (kp and the row stride are multiples of 4)
+  const int kq = kp >> 2;
   int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= m * kp) return;
-  int64_t r = t / kp;
-  int c = (int)(t - r * kp);
-  float v = c < cin ? x[r * stride + c] : 0.f;
-  __nv_bfloat16 hi, lo;
-  split_bf16(v, hi, lo);
-  out[r * 2 * kp + c] = hi;
-  out[r * 2 * kp + kp + c] = lo;
+  if (t >= m * kq) return;
+  int64_t r = t / kq;
+  int c = (int)(t - r * kq) * 4;
+  float v[4];
+  if (c + 3 < cin && (stride & 3) == 0 && ((uintptr_t)x & 15) == 0) {
+    const float4 q = *(const float4*)(x + r * stride + c);
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = c + j < cin ? x[r * stride + c + j] : 0.f;
+  }
+  __nv_bfloat16 hi[4], lo[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) split_bf16(v[j], hi[j], lo[j]);
+  *(uint2*)(out + r * 2 * kp + c) = *(const uint2*)hi;
+  *(uint2*)(out + r * 2 * kp + kp + c) = *(const uint2*)lo;
 }
 
 // weights [kv][cin_pad][cout] fp32 -> Wt [kv][2][kp/16][cout][16] bf16: hi plane then lo plane, and inside a plane one
@@ -753,7 +763,7 @@ extern "C" int gp_student_forward_tc(const gp_student_desc* d, const float* weig
   tc_build_tiles_kernel<<<L.nslab, 256, 0, st>>>(pos, L.S, L.max_tiles, tiles, ntiles, gtile0);
   GP_LAUNCH_CHECK();
   {
-    int64_t tot = m * L.kp0;
+    int64_t tot = m * (L.kp0 / 4);
     tc_split_input_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(x, cin_stride, d->cin[0], L.kp0, m, xin);
     GP_LAUNCH_CHECK();
   }

@@ -14,6 +14,8 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:'gat
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'pool_tc_kernel' -s 4 -c 2 \
    -o gpurun_out/prof_pool -f python bench.py --steps 1 --warmup 0 --pool 1 --no-cpu-baseline > gpurun_out/ncu_pool.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on \
-   -k regex:'lift_mean_kernel|knn_grid_kernel|affinity_softmax_kernel|nn1_query_kernel|scatter_mean_kernel|student_reduce_kernel|pool_tc_plan_kernel|project_views_kernel|gather_gemm_tc_kernel<128>' \
+   -k regex:'lift_mean_kernel|knn_grid_kernel|affinity_softmax_kernel|nn1_query_kernel|scatter_mean_kernel|pool_tc_plan_kernel|project_views_kernel|gather_gemm_tc_kernel<128>|tc_split_input_kernel|logits_split_kernel' \
    -c 14 -o gpurun_out/prof_others -f python bench.py --steps 1 --warmup 0 --pool 1 --no-cpu-baseline > gpurun_out/ncu_others.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'student_reduce_kernel' -s 2 -c 2 \
+   -o gpurun_out/prof_reduce -f python bench.py --steps 1 --warmup 0 --pool 1 --no-cpu-baseline > gpurun_out/ncu_reduce.log 2>&1
 tail -n 3 gpurun_out/pytest_gpu.log; tail -n 2 gpurun_out/smoke.log; tail -n 2 gpurun_out/bench.log | cut -c1-400
