@@ -23,7 +23,10 @@ constexpr int A_STEP = 2 * PT * PK * 2;  // bytes of W (hi + lo) per K-step: 8 K
 constexpr int B_PLANE = PK * PD * 2;     // bytes of one plane of gathered rows per K-step: 16 KB
 constexpr int PSTAGE = A_STEP + 2 * B_PLANE;  // 40 KB
 constexpr int PNSTAGE = 5;
-constexpr int PLAG = 2;
+#ifndef GP_POOL_LAG
+#define GP_POOL_LAG 2
+#endif
+constexpr int PLAG = GP_POOL_LAG;  // cp.async groups (K-steps) a gather warp keeps in flight besides the one it is issuing
 constexpr int P_EPI_LD = 36;
 constexpr int PTHREADS = 384;    // warp 0 W bulk copies, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue, 8-11 row gather
 constexpr int PSMEM = PNSTAGE * PSTAGE + 4 * 32 * P_EPI_LD * 4 + 256 + 1024;
