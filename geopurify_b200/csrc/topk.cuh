@@ -73,6 +73,34 @@ __device__ __forceinline__ KT topk_element(const KT (&v)[4], int e) {
 // merge `nbuf` buffered keys (shared memory) into the sorted list
 template <typename KT>
 __device__ __forceinline__ void topk_flush(KT (&list)[4], const KT* buf, int nbuf, int lane) {
+#ifdef GP_TOPK_SMALL
+  if (nbuf <= 32) {
+    // small batch (end-of-shell leftovers): sort one key per lane (15 compare-exchange steps on a single element
+    // instead of the 28 four-element layers of the 128-key network), then merge.  With the batch sorted ascending in
+    // slots 0..31 of a 128-slot array padded with KMAX, the partner of list element e in the bitonic merge is slot
+    // 127 - e, which is a real key only for e >= 96.
+    KT x = lane < nbuf ? buf[lane] : (KT)~(KT)0;
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+      for (int s = k >> 1; s > 0; s >>= 1) {
+        const KT other = __shfl_xor_sync(0xffffffffu, x, s);
+        const bool lower = (lane & s) == 0;
+        const bool asc = k == 32 ? true : ((lane & k) == 0);
+        const KT mn = x < other ? x : other, mx = x < other ? other : x;
+        x = (lower == asc) ? mn : mx;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int e = lane * 4 + j;
+      const KT rev = __shfl_sync(0xffffffffu, x, (127 - e) & 31);
+      if (e >= 96) list[j] = list[j] < rev ? list[j] : rev;
+    }
+    bitonic_merge128(list, lane);
+    return;
+  }
+#endif
   KT b[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) b[j] = (lane * 4 + j < nbuf) ? buf[lane * 4 + j] : (KT)~(KT)0;
@@ -84,4 +112,3 @@ __device__ __forceinline__ void topk_flush(KT (&list)[4], const KT* buf, int nbu
   }
   bitonic_merge128(list, lane);
 }
-

@@ -185,7 +185,7 @@ __device__ __forceinline__ bool knn_query(const int4* __restrict__ sorted, const
 #pragma unroll
   for (int j = 0; j < 4; ++j) list[j] = KMAX;
   KT thr = KMAX;
-  int nbuf = 0;
+  int nbuf = 0, merged = 0;
   const int rmax = max(cx, max(cy, cz));
   for (int r = 0; r <= rmax; ++r) {
     const int w = 2 * r + 1;
@@ -222,6 +222,7 @@ __device__ __forceinline__ bool knn_query(const int4* __restrict__ sorted, const
           if (nbuf > 96) {
             __syncwarp();
             topk_flush(list, buf, nbuf, lane);
+            merged += nbuf;
             nbuf = 0;
             thr = topk_element(list, K - 1);
             __syncwarp();
@@ -229,10 +230,12 @@ __device__ __forceinline__ bool knn_query(const int4* __restrict__ sorted, const
         }
       }
     }
-    // every voxel within Chebyshev distance g - 1 of the query has now been scanned
-    if (nbuf) {
+    // every voxel within Chebyshev distance g - 1 of the query has now been scanned.  Fewer than K candidates so far:
+    // the search cannot end on this shell, keep buffering instead of paying for a merge.
+    if (nbuf && !(thr == KMAX && merged + nbuf < K && r < rmax)) {
       __syncwarp();
       topk_flush(list, buf, nbuf, lane);
+      merged += nbuf;
       nbuf = 0;
       thr = topk_element(list, K - 1);
       __syncwarp();
