@@ -10,7 +10,7 @@ Two entry styles:
   * `run_scene(SceneInputs)`            -- the B200-first form: cameras + depth instead of precomputed pixel
                                            lists, fused projection/gather, everything stays on the device,
                                            returns labels + IoU histograms.
-Internally voxels are processed in Morton order; every exposed index tensor is in the reference's order.
+Internally voxels are processed in Hilbert-cell order; every exposed index tensor is in the reference's order.
 """
 from __future__ import annotations
 

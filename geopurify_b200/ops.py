@@ -231,7 +231,7 @@ def voxelize(coords, xform):
 
 
 class VoxelIndex:
-    """Morton-sorted voxel order + cell lists (device workspace)."""
+    """Hilbert-cell-sorted voxel order + cell lists (device workspace)."""
 
     def __init__(self, vox_i32, extent=None):
         lib = L.load()

@@ -151,7 +151,7 @@ class AffinityPredictor(nn.Module):
     # -- forward -------------------------------------------------------------------------------
     @torch.no_grad()
     def forward_sorted(self, x, nbr27, normalize=True):
-        """x [M, >=input_stride] fp32 rows in Morton-sorted order (pad columns zero), nbr27 [M,27] int32."""
+        """x [M, >=input_stride] fp32 rows in the voxel index's sorted order (pad columns zero), nbr27 [M,27] int32."""
         L.require_cuda()
         lib = L.load()
         desc, flat = self.pack(x.device)
