@@ -99,46 +99,59 @@ def make_scenes(args, rank):
 
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """nvidia-smi polled every 20 ms from before the warm-up; only samples whose timestamp falls inside the timed
+    region (mark_begin .. mark_end) are reported, so short runs still get clocks taken under load."""
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.proc = index, None
+        self.index, self.proc, self.t0, self.t1 = index, None, None, None
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", "20"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
 
+    def mark_begin(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
+
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.1)
         self.proc.terminate()
         try:
             text, _ = self.proc.communicate(timeout=5)
         except subprocess.TimeoutExpired:
             self.proc.kill()
             text, _ = self.proc.communicate()
-        sm, mx, reasons = [], [], set()
+        import datetime
+        rows = []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in text.strip().splitlines():
             f = [x.strip() for x in line.split(",")]
-            if len(f) < 7:
+            if len(f) < 8:
                 continue
             try:
-                sm.append(float(f[0]))
-                mx.append(float(f[1]))
+                ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                rows.append((ts, float(f[1]), float(f[2]), [n for n, v in zip(names, f[4:8]) if v.lower().startswith("active")]))
             except ValueError:
                 continue
-            for nme, val in zip(names, f[3:7]):
-                if val.lower().startswith("active"):
-                    reasons.add(nme)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        inside = [r for r in rows if self.t0 is not None and self.t0 <= r[0] <= (self.t1 or r[0])]
+        if not inside and rows and self.t0 is not None:   # region shorter than one polling period: nearest sample
+            mid = 0.5 * (self.t0 + (self.t1 or self.t0))
+            inside = [min(rows, key=lambda r: abs(r[0] - mid))]
+        use = inside or rows
+        reasons = sorted({n for r in use for n in r[3]})
+        return {"sm_mhz": float(np.median([r[1] for r in use])) if use else None,
+                "sm_max_mhz": max(r[2] for r in use) if use else None, "samples": len(use), "reasons": reasons}
 
 
 # ----------------------------------------------------------------------------- CPU arm (oracle port)
@@ -314,14 +327,16 @@ def ours_arm(args):
     # ---- device-resident throughput
     # every scene of the pool runs once before timing (first use of a scene size allocates its workspaces)
     warm = max(args.warmup, len(hosts))
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()          # polling starts before the warm-up so that it is up when the timed region begins
     for i in range(warm):
         step_resident(i % len(hosts))
     hist.zero_()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     l0 = _lib.launch_count
+    sampler.mark_begin()
     ms, pts = timed(step_resident, args.steps)
+    sampler.mark_end()
     launches = _lib.launch_count - l0
     clocks = sampler.stop() if rank == 0 else None
     if world > 1:
