@@ -291,3 +291,21 @@ def test_oracle_mining_matches_reference_run(golden_dir):
     pos, neg, _ = oracle.mine_contrastive(feat, g["anchors"], nbr, 63, 48)
     assert np.array_equal(pos.numpy(), g["positive"])
     assert np.array_equal(neg.numpy(), g["negatives"])
+
+
+def test_oracle_projection_and_packing_match_reference_loader_output(golden_dir):
+    """A1-A3 + F2: per-view masks, x_label (rows) and y_label (cols) of the golden scene exactly as the reference's
+    mapper + `scene_based_collate_fn` packed them (tests/golden/scene_lseg.npz)."""
+    g, sc, _ = _oracle_run(golden_dir)
+    W, H = sc.image_dim
+    kmap = oracle.mapper_intrinsics(sc.intrinsics, sc.image_dim)
+    c32 = sc.coords.astype(np.float32)
+    maps = np.stack([oracle.project_view(sc.w2c[v].T.copy(), c32, sc.depth[v], kmap, (W, H), sc.vis_thres, sc.cut)[0]
+                     for v in range(sc.n_views)])
+    kept, rows, cols, pids = oracle.accept_views(maps, 1)
+    assert list(kept) == list(g["kept"])
+    n, V = sc.n_points, len(kept)
+    want_mask = g["mask_2ds"][:, 1].reshape(V, n).astype(bool)
+    assert (maps[:, :, 2].astype(bool) == want_mask).all()
+    assert (np.concatenate(rows) == g["x_labels"]).all() and (np.concatenate(cols) == g["y_labels"]).all()
+    assert (np.concatenate(pids) == np.concatenate([np.nonzero(want_mask[v])[0] for v in range(V)])).all()
