@@ -328,7 +328,8 @@ def affinity_softmax(embed, nbr_sorted, sharpen=20.0):
 
 def pool(f0, D, nbr_sorted, weights, T, tensor_core=None):
     """T applications of the affinity matrix; returns a [m,D] tensor (or f0 itself when T == 0).
-    D == 512 runs on the tensor cores (per-scene plan + tcgen05 block GEMM); other widths one warp per row."""
+    D in (256, 512) runs on the tensor cores (per-scene plan + tcgen05 block GEMM, one 256-column pass per work item);
+    other widths one warp per row."""
     lib = L.load()
     m, k = nbr_sorted.shape
     if T == 0:
@@ -336,7 +337,7 @@ def pool(f0, D, nbr_sorted, weights, T, tensor_core=None):
     if tensor_core is None:
         # the per-scene plan costs about as much as one row-wise application: it pays off from T = 2
         # (profiles/r01_sweep_pool_knn.jsonl)
-        tensor_core = D == 512 and T >= 2
+        tensor_core = D in (256, 512) and T >= 2
     if tensor_core:
         nbp = lib.gp_pool_plan_bytes(m, k)
         plan = _ws(nbp)

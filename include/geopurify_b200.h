@@ -264,11 +264,14 @@ int gp_pool(const float* f0, int64_t stride, int D, const int32_t* nbr_sorted, c
             int K, int T, float* buf_a, float* buf_b, float** out_host, gp_stream_t stream);
 
 /* ---- A10+A11 on the tensor cores (tcgen05 + TMEM): F <- A F as a block-local dense GEMM.  A per-scene plan groups
- * 128 consecutive (Morton-sorted) voxels with the sorted union of their neighbour lists and the dense bf16 hi/lo
- * weight block; every application gathers each union row once per tile and accumulates 128 x 512 fp32 outputs in
- * TMEM (3 bf16 MMAs per product term).  F moves between applications as bf16 hi/lo planes; the last application
- * writes float32.  D must be 512, T >= 1; `nbr_sorted` / `weights` serve tiles whose union exceeds 2048 rows.
- *   out (out) [m, 512] float32;  plan / workspace 256-byte aligned */
+ * 128 consecutive (Hilbert-sorted) voxels with the sorted union of their neighbour lists and keeps the tile's weights
+ * in a compact form (6 bytes per (voxel, neighbour) entry, grouped by 16-row K-step); every application expands the
+ * 128 x 16 weight blocks in shared memory, gathers each union row once per (tile, 256-column half) and accumulates
+ * 128 x 256 fp32 outputs in TMEM (3 bf16 MMAs per product term), two CTAs per SM.  F moves between applications as
+ * bf16 hi/lo planes; the last application writes float32.  D must be 256 or 512, T >= 1; `nbr_sorted` / `weights`
+ * serve tiles whose union exceeds 2048 rows.  Precondition: the K ids of one row are distinct (true for kNN lists;
+ * gp_pool sums duplicates, this path keeps one of them).
+ *   out (out) [m, D] float32;  plan / workspace 256-byte aligned */
 size_t gp_pool_plan_bytes(int64_t m, int K);
 int gp_pool_plan(const int32_t* nbr_sorted, const float* weights, int64_t m, int K, void* plan, size_t plan_bytes,
                  gp_stream_t stream);

@@ -112,6 +112,23 @@ def test_pool_rows_are_convex_combinations():
     assert torch.allclose(out2, 2 * out + 1, atol=1e-4)
 
 
+def test_pool_c_matches_torch_sparse_mm():
+    """spmm_ref.c (the full-size test's pooling oracle) against the reference's own call, torch.sparse.mm."""
+    rng = np.random.default_rng(31)
+    for m, k, d, t in ((700, 96, 518, 19), (257, 16, 33, 3), (97, 96, 8, 1)):
+        e = torch.nn.functional.normalize(torch.randn(m, 128), dim=1)
+        nbr = np.stack([rng.choice(m, k, replace=False) for _ in range(m)])
+        w = oracle.affinity_weights(e, nbr, 20.0, chunk=100)
+        assert torch.equal(w, oracle.affinity_weights(e, nbr, 20.0)), "row chunking changes nothing"
+        f = torch.randn(m, d)
+        f0 = f.clone()
+        a = oracle.pool(f, nbr, w, t)
+        b = oracle.pool_c(f, nbr, w, t)
+        assert torch.equal(f, f0), "pool_c must not touch its input"
+        assert torch.equal(a, b), f"m={m} k={k}: C SpMM differs from torch.sparse.mm by {(a - b).abs().max().item()}"
+        assert torch.equal(a, oracle.pool_c(f, nbr, w, t, visit_order=rng.permutation(m))), "visiting order matters"
+
+
 def test_iou_histograms_match_histc_and_numpy():
     rng = np.random.default_rng(4)
     k = 19

@@ -193,7 +193,7 @@ def test_scene_student_embeddings(scene_run):
     model, ref = scene_run["model"], scene_run["ref"]
     order = model.last["index"].order.long().cpu()
     err = (model.last["embed"].cpu() - ref["embed"][order]).abs().max().item()
-    assert err < 2e-4, f"student embedding max-abs {err}"
+    assert err < 2.5e-5, f"student embedding max-abs {err}"      # measured 2.5e-6 (bf16 hi/lo split): 10x head room
 
 
 def test_scene_softmax_weights(scene_run):
@@ -202,7 +202,7 @@ def test_scene_softmax_weights(scene_run):
     w = model.last["weights"].cpu()
     assert w.shape[1] == 16
     err = (w - ref["weights"][order]).abs().max().item()
-    assert err < 2e-3, f"softmax weight max-abs {err}"     # 20 x amplification of the 2e-4 embedding tolerance
+    assert err < 2e-4, f"softmax weight max-abs {err}"     # 10x the measured error (sharpen 20 amplifies the embeddings')
     assert torch.allclose(w.sum(1), torch.ones(w.shape[0]), atol=1e-5)
 
 
@@ -247,25 +247,25 @@ def test_student_tensor_core_vs_simt_vs_oracle(scene_run):
         errs[prec] = (emb.cpu() - ref["embed"][order]).abs().max().item()
     st.precision = "bf16x3"
     print("student max-abs vs oracle:", errs)
-    assert errs["fp32"] < 2e-5 and errs["bf16x3"] < 2e-4, errs
+    assert errs["fp32"] < 5e-6 and errs["bf16x3"] < 2.5e-5, errs
 
 
-def test_pool_tensor_core_vs_rowwise(gp):
-    """tcgen05 pooling (D=512) against the fp32 one-warp-per-row kernel: clustered neighbour lists, ragged last tile."""
+@pytest.mark.parametrize("D,K,win", [(512, 24, 40), (256, 24, 40), (512, 96, 60), (256, 96, 60)])
+def test_pool_tensor_core_vs_rowwise(gp, D, K, win):
+    """tcgen05 pooling (D = 512 and the APE width 256) against the fp32 one-warp-per-row kernel: clustered neighbour
+    lists, ragged last tile; K=96 puts ~770 entries into a K-step (the expander's register prefetch holds 384)."""
     torch.manual_seed(0)
-    m, K, T = 128 * 9 + 37, 24, 3
-    base = torch.arange(m, device="cuda")[:, None] + torch.arange(-40, 41, device="cuda")[None, :]
-    base = base.clamp(0, m - 1)
-    nb = torch.stack([base[i][torch.randperm(81, device="cuda")] for i in range(m)])
-    nb = torch.stack([torch.unique(nb[i])[:K] if torch.unique(nb[i]).numel() >= K else nb[i][:K] for i in range(m)])
-    nb = nb.int().contiguous()
+    m, T = 128 * 9 + 37, 3
+    base = (torch.arange(m, device="cuda")[:, None] + torch.arange(-win, win + 1, device="cuda")[None, :]) % m
+    nb = torch.stack([base[i][torch.randperm(2 * win + 1, device="cuda")][:K] for i in range(m)]).int().contiguous()
     w = torch.softmax(2 * torch.randn(m, K, device="cuda"), 1).contiguous()
-    f = torch.nn.functional.normalize(torch.randn(m, 512, device="cuda"), dim=1) * 0.7
-    a = gp.pool(f, 512, nb, w, T, tensor_core=True)
-    b = gp.pool(f, 512, nb, w, T, tensor_core=False)
+    f = torch.nn.functional.normalize(torch.randn(m, D, device="cuda"), dim=1) * 0.7
+    a = gp.pool(f, D, nb, w, T, tensor_core=True)
+    b = gp.pool(f, D, nb, w, T, tensor_core=False)
     err = (a - b).abs().max().item()
-    print("pool tc vs rowwise max-abs", err)
+    print(f"pool tc vs rowwise D={D} K={K} max-abs", err)
     assert err < 2e-5
+    assert torch.equal(a, gp.pool(f, D, nb, w, T, tensor_core=True)), "tcgen05 pooling is not deterministic"
 
 
 # ----------------------------------------------------------------------------- A5 consensus lifting
@@ -459,7 +459,8 @@ def test_lift_mean_from_compact_form_equals_dense_fp32(gp, scene_run):
     assert torch.equal(a, b) and torch.equal(sa, sb)
 
 
-def test_pool_tensor_core_union_overflow_falls_back_per_tile(gp):
+@pytest.mark.parametrize("D", [512, 256])
+def test_pool_tensor_core_union_overflow_falls_back_per_tile(gp, D):
     """Tiles whose neighbour union exceeds 2048 rows are served by the row-wise kernel inside gp_pool_tc; mixed with
     compact tiles in one call."""
     torch.manual_seed(1)
@@ -468,9 +469,9 @@ def test_pool_tensor_core_union_overflow_falls_back_per_tile(gp):
     local = (torch.arange(m, device="cuda")[:, None] + torch.arange(1, K + 1, device="cuda")[None, :]) % m
     nb[: 128 * 12] = local[: 128 * 12].int()                                        # compact tiles
     w = torch.softmax(torch.randn(m, K, device="cuda"), 1).contiguous()
-    f = torch.randn(m, 512, device="cuda") * 0.1
-    a = gp.pool(f, 512, nb.contiguous(), w, T, tensor_core=True)
-    b = gp.pool(f, 512, nb.contiguous(), w, T, tensor_core=False)
+    f = torch.randn(m, D, device="cuda") * 0.1
+    a = gp.pool(f, D, nb.contiguous(), w, T, tensor_core=True)
+    b = gp.pool(f, D, nb.contiguous(), w, T, tensor_core=False)
     assert (a - b).abs().max().item() < 2e-5
 
 
