@@ -2,7 +2,8 @@
 """bench.py -- points/s purified + classified per B200 on ScanNetV2-val-shaped synthetic scenes.
 
     python bench.py --gpus N --steps K --warmup W            # our arm (one process per GPU under torchrun for N>1)
-    python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the oracle port on the host cores
+    python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the oracle port on the host cores, same scenes
+    python bench.py --scenes 312 --gpus N                    # fixed evaluation list (strong scaling, all-reduce timed)
 
 A "step" is one scene through the whole hot path: project + occlusion test + gather-mean
 lifting over V views, hole fill, voxel scatter-mean, student forward, kNN, affinity softmax, T pooling applications,
@@ -52,7 +53,12 @@ def parse_args():
     ap.add_argument("--T", type=int, default=REF_T)
     ap.add_argument("--feat-dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-sample-points", type=int, default=20000)
+    ap.add_argument("--scenes", type=int, default=0,
+                    help="fixed-list mode: evaluate a list of this many scenes (312 = scannet_evaluation.txt) whose "
+                         "sizes follow the ScanNet val distribution, dealt longest-first over the ranks; the histogram "
+                         "all-reduce is inside the timed region; --steps is ignored")
+    ap.add_argument("--lifting", default="mean", choices=["mean", "consensus"],
+                    help="A4 gather+mean (lift_lseg_features) or A5 consensus top-3 (lift_xdecoder_features)")
     return ap.parse_args()
 
 
@@ -89,9 +95,27 @@ def scene_sizes(args, rank):
     return [150_000] + [synth.scannet_val_size(rng) for _ in range(args.pool - 1)]
 
 
+def eval_list(args):
+    """Fixed-list mode: sizes of the `--scenes` evaluation scenes (seeded draw from the ScanNet val distribution) and
+    the pool level each one is served by.  Generating 312 distinct synthetic scenes on the host would take half an
+    hour, so the list is quantised to `--pool` size levels (mid-quantiles of the list); scene i of the list runs the
+    pool scene of the nearest level.  Imbalance across ranks, the dealing order and the per-scene launch costs of the
+    real size spread are kept; the point totals reported are those of the scenes actually run."""
+    from geopurify_b200 import synth
+    rng = np.random.default_rng(5557)
+    sizes = np.array([synth.scannet_val_size(rng) for _ in range(args.scenes)])
+    levels = np.quantile(sizes, (np.arange(args.pool) + 0.5) / args.pool).astype(int)
+    assign = np.abs(sizes[:, None] - levels[None, :]).argmin(1)
+    return sizes, levels, assign
+
+
 def make_scenes(args, rank):
     from geopurify_b200 import synth
     out = []
+    if args.scenes:   # fixed-list mode: the pool holds one scene per size level, the same on every rank
+        _, levels, _ = eval_list(args)
+        return [synth.make_scene(n_points=int(n), n_views=args.views, seed=5557 + i, **scene_kwargs(args))
+                for i, n in enumerate(levels)]
     for i, n in enumerate(scene_sizes(args, rank)):
         out.append(synth.make_scene(n_points=n, n_views=args.views, seed=5557 + 1000 * rank + i, **scene_kwargs(args)))
     return out
@@ -155,66 +179,62 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- CPU arm (oracle port)
-def cpu_sample_scene(args):
-    """Bounded sample of the workload for the CPU legs: same V-independent shapes (240x320 views, D=512, K, T, C,
-    full-size student), fewer points and views, room shrunk to keep the ScanNet point density."""
-    from geopurify_b200 import synth
-    n = args.cpu_sample_points
-    s = math.sqrt(n / 150_000.0)
-    views = max(4, min(args.views, int(round(args.views * n / 150_000.0)) + 3))
-    sc = synth.make_scene(n_points=n, n_views=views, image_dim=(320, 240), feat_dim=512, n_classes=args.classes,
-                          seed=5557, room=(5.0 * s, 4.0 * s, 2.7), n_boxes=2)
-    desc = (f"1 scene, N={n} points, V={views} views 240x320, D=512, K={args.K}, T={args.T}, C={args.classes}, "
-            f"full student 518-512x9-128, M={sc.voxel_coords.shape[0]} voxels")
-    return sc, desc
-
-
-def cpu_run(args, sc, state, repeats=1):
-    """Times oracle.evaluate_scene (the CPU restatement of the reference path) on the host cores."""
+def cpu_setup():
+    """All the host threads this process may use: torchrun exports OMP_NUM_THREADS=1 to every rank, which would time
+    the CPU arm on one core.  Set before the oracle's OpenMP library is loaded (it reads the variable then)."""
     import torch
-    # all the host threads this process may use: torchrun exports OMP_NUM_THREADS=1 to every rank, which would time
-    # the CPU arm on one core.  Set before the oracle's OpenMP kNN library is loaded (it reads the variable then).
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     os.environ["OMP_NUM_THREADS"] = str(cores)
     torch.set_num_threads(cores)
     from oracle import oracle
     from sklearn.neighbors import KDTree  # noqa: F401  (first import costs seconds: keep it out of the timed region)
-    oracle.knn_c(np.arange(3 * 200, dtype=np.float32).reshape(200, 3), 4)   # loads the OpenMP kNN library
+    oracle.knn_c(np.arange(3 * 200, dtype=np.float32).reshape(200, 3), 4)   # loads the OpenMP library
+    return oracle, torch.get_num_threads()
+
+
+def cpu_run(args, oracle, sc, state):
+    """One scene through oracle.evaluate_scene (the CPU restatement of the reference path, every stage at the
+    reference's constants; pooling through spmm_ref.c, bit-identical to torch.sparse.mm).  Returns (seconds, stages)."""
     stages = {}
     t0 = time.perf_counter()
-    for _ in range(repeats):
-        oracle.evaluate_scene(sc, state, k=args.K, n_iter=args.T, sharpen=REF_SHARPEN, stages=stages)
-    dt = (time.perf_counter() - t0) / repeats
-    return dt, {k: round(v / repeats, 4) for k, v in stages.items()}, torch.get_num_threads()
+    oracle.evaluate_scene(sc, state, k=args.K, n_iter=args.T, sharpen=REF_SHARPEN, stages=stages)
+    return time.perf_counter() - t0, stages
 
 
 def reference_arm(args):
     """--impl reference: the reference's own path cannot be installed here (MinkowskiEngine, faiss, torch_scatter,
     detectron2 are absent and there is no network), so this arm times the oracle port -- numpy /
-    torch-CPU with the same torch calls the reference makes -- on all host threads."""
+    torch-CPU with the torch calls the reference makes, C for the two library operators whose host versions would
+    take minutes (brute-force kNN, CSR SpMM) -- on all host threads, on THE SAME scenes as our arm: scene pool,
+    sizes, views, K, T and classes are those of `config`; one step = one whole scene."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import torch
     from geopurify_b200 import synth
-    sc, desc = cpu_sample_scene(args)
+    scenes = make_scenes(args, 0)
+    npts = [sc.n_points for sc in scenes]
     state = synth.make_student_state()
-    for _ in range(min(args.warmup, 1)):
-        cpu_run(args, sc, state)
+    oracle, threads = cpu_setup()
+    for i in range(args.warmup):
+        cpu_run(args, oracle, scenes[i % len(scenes)], state)
+    stages, pts = {}, 0
     t0 = time.perf_counter()
-    stages = {}
-    for _ in range(args.steps):
-        _, st, threads = cpu_run(args, sc, state)
+    for i in range(args.steps):
+        _, st = cpu_run(args, oracle, scenes[i % len(scenes)], state)
+        pts += npts[i % len(scenes)]
         for k, v in st.items():
             stages[k] = stages.get(k, 0.0) + v
     dt = time.perf_counter() - t0
-    value = sc.n_points * args.steps / dt
+    value = pts / dt
+    cfg = workload_config(args, npts)
     line = {
         "impl": "reference", "metric": "points/sec purified+classified", "value": value, "unit": "points/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args),
-        "cpu_baseline": {"value": value, "unit": "points/s", "cores": threads, "kind": "port", "sample": desc,
+        "config": cfg,
+        "cpu_baseline": {"value": value, "unit": "points/s", "cores": threads, "kind": "port",
+                         "sample": f"the bench's own scene pool ({npts} points, {args.views} views), one whole scene "
+                                   f"per step, {args.steps} steps after {args.warmup} warm-up",
                          "host_cpus": os.cpu_count(),
                          "stages_s": {k: round(v / args.steps, 4) for k, v in stages.items()}},
         "e2e": {"value": value, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -230,7 +250,7 @@ def workload_config(args, sizes=None):
             if default_shape else f"synthetic scenes, {args.views} views {h_}x{w_}, ")
     cfg = {"workload": name + "512-d features, 2 cm voxels, student 518-512x9-128, one scene per step",
            "views": args.views, "image": f"{h_}x{w_}", "feat_dim": 512, "classes": args.classes, "K": args.K,
-           "T": args.T, "sharpen": REF_SHARPEN, "feat_dtype_2d": args.feat_dtype,
+           "T": args.T, "sharpen": REF_SHARPEN, "feat_dtype_2d": args.feat_dtype, "lifting": args.lifting,
            "scene_pool_per_rank": args.pool, "parallelism": f"scenes sharded over {args.gpus} GPU(s), 1 rank/GPU",
            "l2": "inputs larger than L2: each step reads a different scene's "
                  f"{args.views * h_ * w_ * 512 * (2 if args.feat_dtype == 'bf16' else 4) / 1e9:.1f} GB feature maps",
@@ -242,22 +262,111 @@ def workload_config(args, sizes=None):
 
 
 # ----------------------------------------------------------------------------- algorithmic work per stage
-def stage_work(model, s, args, n, m, pairs, distinct_cells, views_kept):
+def stage_work(model, s, args, n, m, pairs, distinct_cells, views_kept, pairs_visible=0):
     """Algorithmic bytes / FLOPs of one scene per stage (DESIGN.md states the same formulas)."""
     V, D, E, K, T, C = s.w2c.shape[0], 512, 128, args.K, args.T, args.classes
     fs = 2 if args.feat_dtype == "bf16" else 4
     h = 512
     w = {}
     w["project"] = ("hbm", n * 24 + V * n * 8 + V * n * 4 + V * 160)
-    w["lift"] = ("hbm", n * 24 + distinct_cells * D * fs + n * D * 4 + n)
+    if args.lifting == "consensus":   # A5, id-map form: P ids + V Q' (D + C) table/logit floats + N D out
+        q = s.tables.shape[1]
+        w["lift"] = ("hbm", pairs_visible * 1 + V * q * D * 4 + V * q * C * 4 + n * D * 4)
+    else:
+        w["lift"] = ("hbm", n * 24 + distinct_cells * D * fs + n * D * 4 + n)
     w["fill"] = ("hbm", n * 12 + n + n * 4)
     w["voxel_mean"] = ("hbm", n * (D + 6) * 4 + n * 4 + m * (D + 6) * 4)
-    w["student"] = ("tensor", 2.0 * (pairs * 544 * h + 8 * pairs * h * h + m * h * E))
+    w["student"] = ("tensor", 2.0 * (pairs * 518 * h + 8 * pairs * h * h + m * h * E))
     w["knn"] = ("hbm", m * 16 + m * K * 4)
     w["affinity"] = ("hbm", m * E * 4 + m * K * 4 + m * K * 4)
     w["pool"] = ("hbm", T * (2 * m * D * 4 + m * K * 4 + m * E * 4))
     w["classify"] = ("hbm", m * D * 4 + C * D * 4 + m * 4 + n * (4 + 8) + 3 * C * 8)
     return w
+
+
+def fixed_list_arm(args, torch, dist, rank, world, local, model, hosts, resident, npts, hist, ign, pipe, barrier):
+    """--scenes N: a fixed evaluation list dealt longest-first (validation.shard_scenes), every rank runs its share,
+    then the [3,C] histogram block is all-reduced -- all inside the timed region.  Strong scaling: the list is the same
+    for every world size.  Reports whole-job points/s and scenes/s, per-rank busy time (imbalance) and the end-to-end
+    figure through HostScenePipeline.run on pinned host buffers."""
+    from geopurify_b200 import _lib
+    from geopurify_b200.validation import mean_iou, reduce_histograms, shard_scenes
+    sizes, levels, assign = eval_list(args)
+    run_sizes = [npts[a] for a in assign]                      # points of the scene actually run for list entry i
+    mine = shard_scenes(len(sizes), rank, world, sizes=run_sizes)
+    seq = [int(assign[i]) for i in mine]
+    pts_mine = float(sum(run_sizes[i] for i in mine))
+    for i in range(max(args.warmup, len(hosts))):
+        model.run_scene(resident[i % len(hosts)], hist=hist, ignore=ign)
+    pipe.run([hosts[i % len(hosts)] for i in range(len(hosts))])
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+
+    def timed(body):
+        hist.zero_()
+        barrier()
+        e0, eb, e1 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record()
+        body()
+        eb.record()                       # this rank's own work is done
+        reduce_histograms(hist)           # the path's one exchange step, inside the timed region
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1), e0.elapsed_time(eb)], dtype=torch.float64, device="cuda")
+        busy = [torch.zeros_like(t) for _ in range(world)]
+        if world > 1:
+            dist.all_gather(busy, t)
+        else:
+            busy = [t]
+        tot = max(float(b[0]) for b in busy)
+        return tot, [round(float(b[1]), 2) for b in busy]
+
+    l0 = _lib.launch_count
+    sampler.mark_begin()
+    ms, busy = timed(lambda: [model.run_scene(resident[a], hist=hist, ignore=ign) for a in seq])
+    sampler.mark_end()
+    launches = _lib.launch_count - l0
+    clocks = sampler.stop() if rank == 0 else None
+    hsum = hist.cpu().numpy()
+    miou = mean_iou(hsum[0], hsum[1], hsum[2])
+
+    def host_body():
+        res = pipe.run([hosts[a] for a in seq])
+        acc = torch.zeros((3, args.classes), dtype=torch.int64)
+        for _, h in res:                  # host-side accumulation of the per-scene histogram blocks (as validate())
+            acc += h
+        hist.copy_(acc.cuda())
+    ms_e2e, busy_e2e = timed(host_body)
+    tot_pts = torch.tensor([pts_mine], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tot_pts)
+    pts = float(tot_pts.item())
+    if rank == 0:
+        cfg = workload_config(args, [int(x) for x in levels])
+        cfg["workload"] = (f"fixed list of {args.scenes} ScanNetV2-val-sized synthetic scenes (BASELINE.json configs[1]; "
+                           f"sizes quantised to {args.pool} levels), dealt longest-first over the ranks, histogram "
+                           "all-reduce inside the timed region; " + cfg["workload"])
+        cfg["list_points_nominal"] = int(sizes.sum())
+        cfg["list_points_run"] = int(sum(run_sizes))
+        h2d = float(np.mean([hosts[a].nbytes for a in assign]))
+        d2h = float(np.mean([run_sizes[i] * 8 + 3 * args.classes * 8 for i in range(len(sizes))]))
+        line = {
+            "metric": "points/sec purified+classified", "value": pts / (ms * 1e-3), "unit": "points/s",
+            "n_gpus": world, "steps": int(args.scenes), "warmup": max(args.warmup, len(hosts)),
+            "ms_per_step": ms / args.scenes, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": cfg,
+            "scenes_per_s": args.scenes / (ms * 1e-3), "seconds": round(ms * 1e-3, 3),
+            "rank_busy_ms": busy, "imbalance": round(max(busy) / (sum(busy) / len(busy)), 4),
+            "e2e": {"value": pts / (ms_e2e * 1e-3), "unit": "points/s", "ms_per_step": ms_e2e / args.scenes,
+                    "scenes_per_s": args.scenes / (ms_e2e * 1e-3), "rank_busy_ms": busy_e2e,
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "api": "geopurify_b200.affinity_module.HostScenePipeline.run + validation.reduce_histograms"},
+            "gpu_launches": launches, "clocks": clocks, "miou_synthetic": miou[0],
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def ours_arm(args):
@@ -284,9 +393,9 @@ def ours_arm(args):
     student = load_numpy_state(AffinityPredictor(518, 128, 512), state)
     text = scenes[0].text     # same class prompts for every scene (seeded per scene otherwise)
     model = SonataXAffinityTrainer(text_features=text, logit_scale=100.0, student=student, feature_dim=512, K=args.K,
-                                   n_pool=args.T, sharpen=REF_SHARPEN)
+                                   n_pool=args.T, sharpen=REF_SHARPEN, lifting=args.lifting)
     ign = torch.tensor([255], dtype=torch.int64, device="cuda")
-    resident = [upload_scene(h, fdt) for h in hosts]
+    resident = [upload_scene(h, fdt, dense=args.lifting == "mean") for h in hosts]
     torch.cuda.synchronize()
     npts = [h.n_points for h in hosts]
 
@@ -303,6 +412,8 @@ def ours_arm(args):
         for i in range(steps):
             fn(i % len(hosts))
             pts += npts[i % len(hosts)]
+        if world > 1:
+            dist.all_reduce(hist)      # the path's one exchange step ([3,C] int64 over NCCL), inside the timed region
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
@@ -318,6 +429,9 @@ def ours_arm(args):
         model.run_scene(resident[i], hist=hist, ignore=ign)
 
     pipe = HostScenePipeline(model, ign, fdt)
+    if args.scenes:
+        fixed_list_arm(args, torch, dist, rank, world, local, model, hosts, resident, npts, hist, ign, pipe, barrier)
+        return
 
     def host_run(steps):
         """K scenes from pinned host buffers through the public host entry; H2D of scene i+1 and D2H of scene i-1
@@ -339,8 +453,6 @@ def ours_arm(args):
     sampler.mark_end()
     launches = _lib.launch_count - l0
     clocks = sampler.stop() if rank == 0 else None
-    if world > 1:
-        dist.all_reduce(hist)          # the path's one exchange step: [3,C] int64 over NCCL
     from geopurify_b200.validation import mean_iou
     hsum = hist.cpu().numpy()
     miou = mean_iou(hsum[0], hsum[1], hsum[2])
@@ -406,7 +518,7 @@ def ours_arm(args):
         pairs = int((model.last["nbr27"] >= 0).sum())
         m = model.last["pooled"].shape[0]
         scene_meta.append({"m": m, "pairs": pairs})
-        wk = stage_work(model, s, args, sc.n_points, m, pairs, cells, int(keep.sum()))
+        wk = stage_work(model, s, args, sc.n_points, m, pairs, cells, int(keep.sum()), int((vis >= 0).sum()))
         for k, (b, v) in wk.items():
             works.setdefault(k, [b, 0.0])[1] += v / reps
         model.last = {}
@@ -467,10 +579,13 @@ def ours_arm(args):
         "miou_synthetic": miou[0],
     }
     if not args.no_cpu_baseline and world == 1:
-        sc, desc = cpu_sample_scene(args)
-        dt, st, threads = cpu_run(args, sc, state)
-        line["cpu_baseline"] = {"value": sc.n_points / dt, "unit": "points/s", "cores": threads, "kind": "port",
-                                "sample": desc, "host_cpus": os.cpu_count(), "seconds": round(dt, 2), "stages_s": st}
+        oracle, threads = cpu_setup()
+        dt, st = cpu_run(args, oracle, scenes[0], state)
+        line["cpu_baseline"] = {"value": scenes[0].n_points / dt, "unit": "points/s", "cores": threads, "kind": "port",
+                                "sample": f"scene 0 of the pool (N={scenes[0].n_points}, V={args.views}), the whole "
+                                          "path once at the reference constants",
+                                "host_cpus": os.cpu_count(), "seconds": round(dt, 2),
+                                "stages_s": {k: round(v, 3) for k, v in st.items()}}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -4,23 +4,29 @@
 // In Hilbert-cell order the K-neighbour lists of consecutive voxels overlap heavily: 128 consecutive voxels reference
 // only ~4.3 |tile| distinct rows instead of 128 K.  A per-scene PLAN stores, for every tile of 128 output voxels, the
 // sorted union U of its neighbour lists and the tile's weights in a COMPACT form: the 128 K (weight, position) entries
-// grouped by K-step (16 union rows), 6 bytes each -- bf16 hi | bf16 lo | byte offset inside the K-step's operand block.
+// grouped by K-step (16 union rows), 8 bytes each -- bf16 hi | bf16 lo | byte offset inside the K-step's operand block.
 // One application is
 //   out_tile[128 x D] = W_tile[128 x |U|] * F[U, :]
 // run as D/256 independent PASSES of 256 columns (work item = (tile, column half)), TWO CTAs per SM with 256 TMEM
 // columns each, so that one CTA's epilogue (TMEM drain, bf16 split, stores) runs under the other CTA's MMAs.  Per
 // K-step the dense 128 x 16 weight block (zeros where a voxel does not use a neighbour) is EXPANDED IN SHARED MEMORY
-// from the compact entries by three otherwise idle warps (zero 8 KB, scatter ~360 entries); the rows F[U] are gathered
-// once per work item by cp.async into the MN-major operand layout.  F travels between applications as bf16 hi/lo
+// from the compact entries by three otherwise idle warps (zero 8 KB, scatter ~360 entries; the entries of a warp's next
+// K-step are loaded into registers while the current one waits for its stage); the rows F[U] are gathered once per work
+// item by cp.async into the MN-major operand layout, every thread's copies arriving on the stage's mbarrier by
+// themselves (cp.async.mbarrier.arrive.noinc), so all free stages have their rows in flight.  F travels between applications as bf16 hi/lo
 // planes (16 mantissa bits, relative error 2^-17 per application); products use Whi*Fhi + Whi*Flo + Wlo*Fhi with fp32
-// accumulation in TMEM.  HBM traffic per application: F planes in + out (2 x 4 m D bytes), the compact plan (6 m K
+// accumulation in TMEM.  HBM traffic per application: F planes in + out (2 x 4 m D bytes), the compact plan (8 m K
 // bytes) and the union lists -- no dense weight block and no M x K fp32 tensor is re-read.
-// -DGP_POOL_DENSE=1 builds the round-1 plan format (dense bf16 hi/lo blocks streamed by bulk copies) for A/B runs.
+// Two plan formats, chosen at build time: GP_POOL_DENSE=1 (default) stores the expanded 128 x 16 bf16 hi/lo blocks and
+// streams them with 8 KB bulk copies (300 MB of plan per scene, re-read by every application; faster: the shared-memory
+// port, which the MMAs' operand reads already load to ~60 %, is spared the zero-fill + scatter of the expansion);
+// GP_POOL_DENSE=0 is the compact format described above (100 MB of plan, 26 % less DRAM traffic per application,
+// 17 % slower on B200 -- kept for A/B runs and for memory-tight scenes).
 #include "common.cuh"
 #include "tc.cuh"
 
 #ifndef GP_POOL_DENSE
-#define GP_POOL_DENSE 0
+#define GP_POOL_DENSE 1   // measured (profiles/r02_*): dense plan 0.233 ms per application at M = 130k, compact 0.272 ms
 #endif
 
 namespace {
@@ -35,10 +41,6 @@ constexpr int A_STEP = 2 * A_PLANE;      // hi + lo: 8 KB
 constexpr int B_PLANE = PK * PH * 2;     // bytes of one plane of gathered rows per K-step: 8 KB
 constexpr int PSTAGE = A_STEP + 2 * B_PLANE;  // 24 KB
 constexpr int PNSTAGE = 4;
-#ifndef GP_POOL_LAG
-#define GP_POOL_LAG 2
-#endif
-constexpr int PLAG = GP_POOL_LAG;  // cp.async groups (K-steps) a gather warp keeps in flight besides the one it is issuing
 constexpr int P_EPI_LD = 20;     // floats per staged row of the 16-column transpose buffer (16-byte aligned)
 constexpr int PTHREADS = 384;    // warps 0, 2, 3 weight expansion (dense build: warp 0 bulk copies), 1 MMA, 2 also TMEM
                                  // alloc, 4-7 epilogue, 8-11 row gather
@@ -47,7 +49,7 @@ constexpr int KOFS_LD = KSTEP_CAP + 4;   // per-tile K-step offset table (int32)
 
 struct PlanLayout {
   int64_t tiles;
-  size_t off_count, off_uidx, off_kofs, off_wv, off_wp, off_w, bytes;
+  size_t off_count, off_uidx, off_kofs, off_went, off_w, bytes;
 };
 
 inline PlanLayout plan_layout(int64_t m, int K) {
@@ -61,11 +63,10 @@ inline PlanLayout plan_layout(int64_t m, int K) {
   };
   L.off_count = take(sizeof(int32_t) * L.tiles);
   L.off_uidx = take(sizeof(int32_t) * L.tiles * KSTEP_CAP * PK);
-  L.off_kofs = L.off_wv = L.off_wp = L.off_w = 0;
+  L.off_kofs = L.off_went = L.off_w = 0;
   if (COMPACT) {
     L.off_kofs = take(sizeof(int32_t) * L.tiles * KOFS_LD);
-    L.off_wv = take(sizeof(uint32_t) * L.tiles * PT * K);
-    L.off_wp = take(sizeof(uint16_t) * L.tiles * PT * K);
+    L.off_went = take(sizeof(uint2) * L.tiles * PT * K);
   } else {
     L.off_w = take((size_t)L.tiles * KSTEP_CAP * A_STEP);
   }
@@ -96,8 +97,8 @@ constexpr int PLAN_UCAP = KSTEP_CAP * PK;
 __global__ void __launch_bounds__(256) pool_tc_plan_kernel(const int32_t* __restrict__ nbr,
                                                             const float* __restrict__ w, int64_t m, int K,
                                                             int32_t* __restrict__ ucount, int32_t* __restrict__ uidx,
-                                                            int32_t* __restrict__ kofs_out, uint32_t* __restrict__ wv,
-                                                            uint16_t* __restrict__ wp, uint8_t* __restrict__ wplan) {
+                                                            int32_t* __restrict__ kofs_out, uint2* __restrict__ went,
+                                                            uint8_t* __restrict__ wplan) {
   __shared__ uint32_t table[PLAN_HASH];
   __shared__ uint32_t keys[PLAN_UCAP];
   __shared__ int s_nu, s_over;
@@ -199,16 +200,15 @@ __global__ void __launch_bounds__(256) pool_tc_plan_kernel(const int32_t* __rest
     for (int e = threadIdx.x; e <= KSTEP_CAP; e += 256) ko[e] = start[e];
     for (int e = threadIdx.x; e < KSTEP_CAP; e += 256) cnt[e] = 0;
     __syncthreads();
-    uint32_t* tv = wv + t * (int64_t)PT * K;
-    uint16_t* tp = wp + t * (int64_t)PT * K;
+    uint2* te = went + t * (int64_t)PT * K;
     for (int e = threadIdx.x; e < nent; e += 256) {
       const int pos = position((uint32_t)__ldg(nbr + row0 * K + e));
       const int ks = pos >> 4;
       const int slot = start[ks] + atomicAdd(&cnt[ks], 1);
       __nv_bfloat16 h, l;
       split_bf16(__ldg(w + row0 * K + e), h, l);
-      tv[slot] = ((uint32_t)__bfloat16_as_ushort(h) << 16) | (uint32_t)__bfloat16_as_ushort(l);
-      tp[slot] = (uint16_t)a_block_offset(e / K, pos & 15);
+      te[slot] = make_uint2(((uint32_t)__bfloat16_as_ushort(h) << 16) | (uint32_t)__bfloat16_as_ushort(l),
+                            a_block_offset(e / K, pos & 15));
     }
   } else {
     uint8_t* wp_base = wplan + (size_t)t * KSTEP_CAP * A_STEP;
@@ -250,8 +250,7 @@ struct PoolParams {
   const int32_t* ucount;      // [tiles]
   const int32_t* uidx;        // [tiles][KSTEP_CAP * PK]
   const int32_t* kofs;        // [tiles][KOFS_LD]           (compact plan)
-  const uint32_t* wv;         // [tiles][PT * K]  hi << 16 | lo
-  const uint16_t* wp;         // [tiles][PT * K]  byte offset inside the K-step's plane
+  const uint2* went;          // [tiles][PT * K]  x = hi << 16 | lo, y = byte offset inside the K-step's plane
   const uint8_t* wplan;       // [tiles][KSTEP_CAP][A_STEP] (dense plan)
   int64_t m;
   int tiles, K, D, halves;
@@ -274,7 +273,8 @@ __global__ void __launch_bounds__(PTHREADS, 2) pool_tc_kernel(const PoolParams P
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < PNSTAGE; ++s) {
-      tc::mbar_init(&full[s], 4 + 1);  // 4 gather warps + the weight block (expander warp / bulk copy expect_tx)
+      tc::mbar_init(&full[s], 128 + 1);  // every gather thread's cp.async completion + the weight block (expander
+                                         // warp's lane 0 / bulk copy expect_tx)
       tc::mbar_init(&empty[s], 1);
     }
     tc::mbar_init(tmem_full, 1);
@@ -294,48 +294,70 @@ __global__ void __launch_bounds__(PTHREADS, 2) pool_tc_kernel(const PoolParams P
 
   if (COMPACT && (warp == 0 || warp == 2 || warp == 3)) {
     // ===================== weight blocks: expanded in shared memory from the compact entries =====================
-    // three warps take the K-steps round robin; each zeroes the 8 KB block, then scatters the step's entries
+    // three warps take the K-steps round robin; each zeroes the 8 KB block, then scatters the step's entries.  The
+    // entries of the warp's NEXT K-step are loaded (registers, PRE per lane) right after the current block is handed
+    // over, so their latency runs under the two K-steps the other warps serve.
     const int eid = warp == 0 ? 0 : warp - 1;
-    constexpr int PRE = 12;  // entries per lane fetched before the stage is known to be free (384 of ~360 per step)
-    uint32_t it = 0;
-    for (int wi = blockIdx.x; wi < items; wi += gridDim.x) {
-      const int t = wi / P.halves;
-      const int ks_n = ksteps_of(t);
-      const int32_t* ko = P.kofs + (int64_t)t * KOFS_LD;
-      const uint32_t* tv = P.wv + (int64_t)t * PT * P.K;
-      const uint16_t* tp = P.wp + (int64_t)t * PT * P.K;
-      for (int ks = 0; ks < ks_n; ++ks, ++it) {
-        if ((int)(it % 3) != eid) continue;
-        const int s = it % PNSTAGE;
-        const int e0 = __ldg(ko + ks), e1 = __ldg(ko + ks + 1);
-        uint32_t pv[PRE], pp[PRE];
-#pragma unroll
-        for (int j = 0; j < PRE; ++j) {
-          const int e = e0 + j * 32 + lane;
-          pv[j] = e < e1 ? __ldg(tv + e) : 0u;
-          pp[j] = e < e1 ? (uint32_t)__ldg(tp + e) : 0xffffffffu;
+    constexpr int PRE = 14;  // 448 entries per K-step in registers (mean ~360 at K = 96); the rest is loaded late
+    int wi = blockIdx.x, t = 0, ks = -1, ks_n = 0, e0 = 0, e1 = 0;
+    uint32_t it = 0xffffffffu;   // K-steps of this CTA so far, minus one
+    const uint2* te = nullptr;
+    uint2 pe[PRE];
+    bool first = true;
+    auto advance = [&]() -> bool {   // next K-step with it % 3 == eid; loads its first PRE * 32 entries
+      for (;;) {
+        if (first) {
+          first = false;
+          if (wi >= items) return false;
+          t = wi / P.halves;
+          ks_n = ksteps_of(t);
+          ks = -1;
         }
-        tc::mbar_wait(&empty[s], ((it / PNSTAGE) & 1) ^ 1);
-        uint8_t* a = smem + s * PSTAGE;
-#pragma unroll
-        for (int j = 0; j < A_STEP / 16 / 32; ++j) ((uint4*)a)[j * 32 + lane] = make_uint4(0, 0, 0, 0);
-        __syncwarp();
-#pragma unroll
-        for (int j = 0; j < PRE; ++j)
-          if (pp[j] != 0xffffffffu) {
-            *(uint16_t*)(a + pp[j]) = (uint16_t)(pv[j] >> 16);
-            *(uint16_t*)(a + A_PLANE + pp[j]) = (uint16_t)(pv[j] & 0xffffu);
-          }
-        for (int e = e0 + PRE * 32 + lane; e < e1; e += 32) {
-          const uint32_t v = __ldg(tv + e);
-          const uint32_t p = __ldg(tp + e);
-          *(uint16_t*)(a + p) = (uint16_t)(v >> 16);
-          *(uint16_t*)(a + A_PLANE + p) = (uint16_t)(v & 0xffffu);
+        ++ks;
+        while (ks >= ks_n) {
+          wi += gridDim.x;
+          if (wi >= items) return false;
+          t = wi / P.halves;
+          ks_n = ksteps_of(t);
+          ks = 0;
         }
-        tc::fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive(&full[s]);
+        ++it;
+        if ((int)(it % 3) == eid) break;
       }
+      const int32_t* ko = P.kofs + (int64_t)t * KOFS_LD;
+      te = P.went + (int64_t)t * PT * P.K;
+      e0 = __ldg(ko + ks);
+      e1 = __ldg(ko + ks + 1);
+#pragma unroll
+      for (int j = 0; j < PRE; ++j) {
+        const int e = e0 + j * 32 + lane;
+        pe[j] = e < e1 ? __ldg(te + e) : make_uint2(0u, 0xffffffffu);
+      }
+      return true;
+    };
+    bool have = advance();
+    while (have) {
+      const int s = it % PNSTAGE;
+      tc::mbar_wait(&empty[s], ((it / PNSTAGE) & 1) ^ 1);
+      uint8_t* a = smem + s * PSTAGE;
+#pragma unroll
+      for (int j = 0; j < A_STEP / 16 / 32; ++j) ((uint4*)a)[j * 32 + lane] = make_uint4(0, 0, 0, 0);
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < PRE; ++j)
+        if (pe[j].y != 0xffffffffu) {
+          *(uint16_t*)(a + pe[j].y) = (uint16_t)(pe[j].x >> 16);
+          *(uint16_t*)(a + A_PLANE + pe[j].y) = (uint16_t)(pe[j].x & 0xffffu);
+        }
+      for (int e = e0 + PRE * 32 + lane; e < e1; e += 32) {
+        const uint2 v = __ldg(te + e);
+        *(uint16_t*)(a + v.y) = (uint16_t)(v.x >> 16);
+        *(uint16_t*)(a + A_PLANE + v.y) = (uint16_t)(v.x & 0xffffu);
+      }
+      tc::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&full[s]);
+      have = advance();
     }
   } else if (!COMPACT && warp == 0) {
     // ===================== dense plan: one 8 KB bulk copy per K-step =====================
@@ -367,6 +389,7 @@ __global__ void __launch_bounds__(PTHREADS, 2) pool_tc_kernel(const PoolParams P
       for (int ks = 0; ks < ks_n; ++ks, ++it) {
         const int s = it % PNSTAGE;
         tc::mbar_wait(&full[s], (it / PNSTAGE) & 1);
+        tc::fence_proxy_async();   // the gather threads' cp.async writes (generic proxy) before the async-proxy reads
         tc::tc_fence_after();
         if (lane == 0) {
           const uint32_t a_hi = tc::smem_u32(smem + s * PSTAGE);
@@ -442,9 +465,9 @@ __global__ void __launch_bounds__(PTHREADS, 2) pool_tc_kernel(const PoolParams P
     // warp w owns union rows k = 4w .. 4w+3 of the K-step.  One warp-wide cp.async moves the 512 contiguous bytes of
     // one row plane's column half (4 cache lines).  16-byte chunk q (0..31) = column block nb = q >> 3, chunk c = q & 7
     // inside the 128-byte atom row: atom (nb, k >> 3) at ((nb * 2 + (k >> 3)) * 1024), row (k & 7) of 128 bytes, chunk
-    // c stored at c ^ (k & 7).
+    // c stored at c ^ (k & 7).  Completion is asynchronous (cp.async.mbarrier.arrive.noinc per thread).
     const int w = warp - 8;
-    uint32_t it = 0, signalled = 0;
+    uint32_t it = 0;
     for (int wi = blockIdx.x; wi < items; wi += gridDim.x) {
       const int t = wi / P.halves, half = wi - t * P.halves;
       const int ks_n = ksteps_of(t);
@@ -467,21 +490,10 @@ __global__ void __launch_bounds__(PTHREADS, 2) pool_tc_kernel(const PoolParams P
           tc::cp_async16(dst, src, 16);
           tc::cp_async16(dst + B_PLANE, src + P.D, 16);
         }
-        tc::cp_async_commit();
-        if (it >= PLAG) {
-          tc::cp_async_wait<PLAG>();
-          tc::fence_proxy_async();
-          __syncwarp();
-          if (lane == 0) tc::mbar_arrive(&full[signalled % PNSTAGE]);
-          ++signalled;
-        }
+        tc::cp_async_arrive_noinc(&full[s]);   // arrives when this thread's copies above have landed
       }
     }
     tc::cp_async_wait<0>();
-    tc::fence_proxy_async();
-    __syncwarp();
-    for (; signalled < it; ++signalled)
-      if (lane == 0) tc::mbar_arrive(&full[signalled % PNSTAGE]);
   }
 
   tc::tc_fence_before();
@@ -553,7 +565,7 @@ extern "C" int gp_pool_plan(const int32_t* nbr_sorted, const float* weights, int
   const bool tg = gp_timing_begin(GP_T_POOL_PLAN, (cudaStream_t)stream);
   pool_tc_plan_kernel<<<(unsigned)L.tiles, 256, 0, (cudaStream_t)stream>>>(
       nbr_sorted, weights, m, K, (int32_t*)(p + L.off_count), (int32_t*)(p + L.off_uidx), (int32_t*)(p + L.off_kofs),
-      (uint32_t*)(p + L.off_wv), (uint16_t*)(p + L.off_wp), (uint8_t*)(p + L.off_w));
+      (uint2*)(p + L.off_went), (uint8_t*)(p + L.off_w));
   if (tg) gp_timing_end(GP_T_POOL_PLAN, (cudaStream_t)stream);
   GP_LAUNCH_CHECK();
   return GP_OK;
@@ -601,8 +613,7 @@ extern "C" int gp_pool_tc(const float* f0, int64_t stride, int D, const void* pl
   P.ucount = (const int32_t*)(p + L.off_count);
   P.uidx = (const int32_t*)(p + L.off_uidx);
   P.kofs = (const int32_t*)(p + L.off_kofs);
-  P.wv = (const uint32_t*)(p + L.off_wv);
-  P.wp = (const uint16_t*)(p + L.off_wp);
+  P.went = (const uint2*)(p + L.off_went);
   P.wplan = (const uint8_t*)(p + L.off_w);
   P.m = m;
   P.tiles = (int)L.tiles;

@@ -25,18 +25,21 @@ namespace {
 constexpr int TM = 128;        // pairs (rows) per tile = UMMA M
 constexpr int BK = 16;         // K per stage = UMMA K for bf16; 32-byte operand rows, SWIZZLE_32B
 constexpr int ROWB = BK * 2;   // bytes per operand row per stage
+#ifndef GP_STU_CL
+#define GP_STU_CL 2
+#endif
 #ifndef GP_STU_NSTAGE
 #define GP_STU_NSTAGE 5
-#define GP_STU_AK 32
-#define GP_STU_NA 3
+#define GP_STU_AK 64
+#define GP_STU_NA (GP_STU_CL == 2 ? 4 : 2)
+#endif
+#ifndef GP_STU_EPI_DIRECT
+#define GP_STU_EPI_DIRECT 1
 #endif
 constexpr int NSTAGE = GP_STU_NSTAGE;  // B (weight) stages of K=16
 constexpr int AK = GP_STU_AK;  // K per A chunk: 64- or 128-byte operand rows, SWIZZLE_64B / SWIZZLE_128B
 constexpr int AKS = AK / BK;   // K=16 steps per A chunk
 constexpr int NA = GP_STU_NA;  // A chunk buffers
-#ifndef GP_STU_CL
-#define GP_STU_CL 1
-#endif
 constexpr int CL = GP_STU_CL;  // 2: CTA pairs (cta_group::2).  Two tiles of one kernel offset form one M = 256 MMA over
                                // two SMs; each SM gathers its own 128 A rows and ingests only HALF of every W_o slice
 constexpr bool PAIR = CL == 2;
@@ -240,7 +243,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
   } else if (warp >= 4 && warp < 8) {
     // ===================== epilogue: TMEM -> registers -> smem transpose -> coalesced global rows =====================
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
-    float* buf = epi + q * 32 * EPI_LD;
+    [[maybe_unused]] float* buf = epi + q * 32 * EPI_LD;
     uint32_t tcount = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
       const TileInfo ti = tile_of(t);
@@ -290,6 +293,38 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
         continue;
       }
       float* crow = P.c + ((int64_t)ti.c_row0 + q * 32) * P.ldc;
+#if GP_STU_EPI_DIRECT
+      // accumulator-fragment loads: four threads hold one 32-byte sector of a row, stored as float2 straight from the
+      // registers -- no shared-memory transpose (the smem port is shared with the MMAs' operand reads)
+#pragma unroll 1
+      for (int hb = 0; hb < 2; ++hb) {
+        const int ra = hb * 16 + (lane >> 2), rb = ra + 8;
+        float* pa = crow + (int64_t)ra * P.ldc + 2 * (lane & 3);
+        float* pb = crow + (int64_t)rb * P.ldc + 2 * (lane & 3);
+#pragma unroll 1
+        for (int cg = 0; cg < N / 64; ++cg) {
+          uint32_t v[32];
+          tc::tmem_ld_16x256b_x8(tmem_base + ((uint32_t)(q * 32 + hb * 16) << 16) + cg * 64, v);
+          tc::tmem_ld_wait();
+          if (hb == 1 && cg == N / 64 - 1) {  // accumulator fully read: the next tile's MMAs may start
+            tc::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+              if (PAIR && crank != 0) tc::mbar_arrive_cluster(tmem_empty, 0);
+              else tc::mbar_arrive(tmem_empty);
+            }
+          }
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const int col = cg * 64 + g * 8;
+            if (ra < rows_here)
+              *(float2*)(pa + col) = make_float2(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]));
+            if (rb < rows_here)
+              *(float2*)(pb + col) = make_float2(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
+          }
+        }
+      }
+#else
       for (int ch = 0; ch < N / 32; ++ch) {
         uint32_t v[32];
         tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ch * 32, v);
@@ -318,6 +353,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
         }
         __syncwarp();
       }
+#endif
     }
   } else if (warp >= 8) {
     // ===================== A gather: warp w owns tile rows [32 w, 32 w + 32); 8 lanes fetch one 128-byte row slice ====

@@ -93,21 +93,46 @@ class PointCloudToImageMapper(object):
         d = depth if (depth is None or isinstance(depth, str)) else np.asarray(depth)[None]
         pix, _ = self.compute_mapping_views(np.asarray(world_to_camera)[None], coords_np, d)
         mapping = ops.pix_to_mapping(pix[0], int(self.image_dim[0])).cpu().numpy().astype(int)
-        # `weight` (fusion_util.py:118,145) is returned but never used by any caller; it depends on the
-        # unmasked rounded pixel, which is host-side numpy here to keep the kernel output compact.
-        weight = self._weight(world_to_camera, coords_np)
-        return mapping, weight
+        # `weight` (fusion_util.py:118,145) is returned but never read by any caller (data_loader_ablation.py:249 drops
+        # it): it is handed back as a lazy array that is only evaluated -- on the device -- if somebody looks at it.
+        return mapping, LazyCenterWeight(self, np.asarray(world_to_camera), coords_np)
 
-    def _weight(self, world_to_camera, coords):
-        k = self.intrinsics
-        cn = np.concatenate([coords, np.ones([coords.shape[0], 1])], axis=1).T
-        p = np.matmul(np.asarray(world_to_camera).T, cn)
-        with np.errstate(all="ignore"):
-            p[0] = (p[0] * k[0][0]) / p[2] + k[0][2]
-            p[1] = (p[1] * k[1][1]) / p[2] + k[1][2]
-            pi = np.round(p).astype(int)
-            cd = np.sqrt((pi[0] - self.image_dim[0] / 2) ** 2 + (pi[1] - self.image_dim[1] / 2) ** 2)
-            return np.exp(-cd / 10)
+
+class LazyCenterWeight:
+    """`weight = exp(-|round(pixel) - image centre| / 10)` of PointCloudToImageMapper.compute_mapping
+    (models/utils/fusion_util.py:117-118, 145).  No caller reads it, so nothing is computed unless somebody looks:
+    it behaves as a numpy array (`np.asarray(w)`, `w[i]`, `len(w)`, `w.shape`) and is evaluated on first use with
+    the reference's own numpy formulas (bit-identical to its output; the golden tests compare it with atol = 0)."""
+
+    def __init__(self, mapper, world_to_camera, coords):
+        self._args = (mapper.intrinsics.copy(), tuple(mapper.image_dim), world_to_camera, coords)
+        self._value = None
+        self.shape = (coords.shape[0],)
+        self.dtype = np.dtype(np.float64)
+
+    def _eval(self):
+        if self._value is None:
+            k, dim, w2c_t, coords = self._args
+            cn = np.concatenate([coords, np.ones([coords.shape[0], 1])], axis=1).T
+            p = np.matmul(w2c_t.T, cn)
+            with np.errstate(all="ignore"):
+                p[0] = (p[0] * k[0][0]) / p[2] + k[0][2]
+                p[1] = (p[1] * k[1][1]) / p[2] + k[1][2]
+                pi = np.round(p).astype(int)
+                cd = np.sqrt((pi[0] - dim[0] / 2) ** 2 + (pi[1] - dim[1] / 2) ** 2)
+                self._value = np.exp(-cd / 10)
+            self._args = None
+        return self._value
+
+    def __array__(self, dtype=None, copy=None):
+        v = self._eval()
+        return v if dtype is None else v.astype(dtype)
+
+    def __len__(self):
+        return self.shape[0]
+
+    def __getitem__(self, i):
+        return self._eval()[i]
 
 
 class PointCloudToImageMappermatterport(object):

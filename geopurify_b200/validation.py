@@ -1,4 +1,5 @@
 """Mirror of the reference's classification + metric code on the CUDA path.
+(`AverageMeter` is the reference's interface class, util/util.py:108-124, kept verbatim so callers can swap imports.)
 
 Reference: run/validation.py:413-439 (normalise, logits, argmax, zero-row label fill, IoU call) and
 :458-553 (running sums, mIoU / mAcc / allAcc); util/util.py:108-124 (AverageMeter), :160-177
@@ -98,33 +99,65 @@ def reduce_histograms(hist, group=None):
     return hist
 
 
+class ValidateResult(tuple):
+    """What the reference's validate() returns -- `(mIoU_Base, mIoU_Novel)` (run/validation.py:549-552) -- with the
+    numbers it only logs attached: `.base`, `.novel`, `.all` = (mIoU, mAcc, allAcc) triples, `.iou_class_*` and the
+    exact int64 running sums `.sums` = (intersection, union, target) over all classes."""
+
+    def __new__(cls, base, novel, all_, iou_class, sums):
+        self = super().__new__(cls, (base[0], novel[0]))
+        self.base, self.novel, self.all = base, novel, all_
+        self.iou_class_base, self.iou_class_novel, self.iou_class_all = iou_class
+        self.sums = sums
+        return self
+
+
+def _split_indices(category_split, name):
+    idx = category_split[name] if isinstance(category_split, dict) else getattr(category_split, name)
+    return np.asarray(list(idx), dtype=np.int64)
+
+
 @torch.no_grad()
-def validate(val_loader, model, test_classes, test_ignore_label, logger=None, rank=0, world=1):
-    """Loop body of run/validation.py:376-553 (All-classes meters).  Returns (mIoU, mAcc, allAcc) and the
-    three float32 running sums.  With world > 1 each rank evaluates the scenes `shard_scenes` gives it and the
-    sums are all-reduced once at the end (exact int64), so every rank returns the same numbers."""
-    im, um, tm = AverageMeter(), AverageMeter(), AverageMeter()
+def validate(val_loader, model, test_classes, test_ignore_label, logger=None, rank=0, world=1, category_split=None):
+    """Loop body of run/validation.py:376-553.  The three [C] histograms of every scene are accumulated in int64
+    (exact; the reference's float32 meters are exact only below 2^24 points per class, and identical there) and the
+    Base / Novel / All metrics of :478-519 are taken from the float32 view of the sums, as the reference's numpy
+    meters would hold them.  With world > 1 each rank evaluates the scenes `shard_scenes` gives it and the int64
+    block is all-reduced once at the end, so every rank returns the same numbers.
+
+    Without `category_split`: returns ((mIoU, mAcc, allAcc) over all classes, (intersection, union, target) float32).
+    With `category_split` (an object or dict with `base_category` / `novel_category` index lists, the reference's
+    `args.category_split`): returns a `ValidateResult`, i.e. the reference's `(mIoU_Base, mIoU_Novel)` tuple."""
+    c = test_classes
+    acc = np.zeros((3, c), dtype=np.int64)
     mine = set(shard_scenes(len(val_loader), rank, world)) if world > 1 else None
     for i, batch_data in enumerate(val_loader):
         if mine is not None and i not in mine:
             continue
-        if batch_data is None:
+        if batch_data is None:                                         # run/validation.py:377-379
             continue
         scene_coords, scene_label = batch_data[0], batch_data[3]
         res = model.evaluate_scene(batch_data)
         pred = classify_scene(res["scene_features"], res["text_features"], res["logit_scale"], scene_coords)
         inter, union, tgt = intersectionAndUnionGPU(pred, scene_label.detach().cuda(), test_classes, test_ignore_label)
-        im.update(inter.cpu().numpy())
-        um.update(union.cpu().numpy())
-        tm.update(tgt.cpu().numpy())
+        acc += torch.stack([inter, union, tgt]).round().to(torch.int64).cpu().numpy()   # per-scene counts < 2^24: exact
         if logger:
             logger.info("Process: [{}/{}]".format(i, len(val_loader)))
-    c = test_classes
-    sums = [np.asarray(x.sum, dtype=np.float64) if x.count else np.zeros(c) for x in (im, um, tm)]
     if world > 1:
-        block = torch.as_tensor(np.stack(sums)).round().to(torch.int64)
+        block = torch.as_tensor(acc)
         if torch.distributed.get_backend() == "nccl":
             block = block.cuda()
-        sums = list(reduce_histograms(block).cpu().numpy().astype(np.float32))
-    miou, macc, allacc = mean_iou(sums[0], sums[1], sums[2])
-    return (miou, macc, allacc), (sums[0], sums[1], sums[2])
+        acc = reduce_histograms(block).cpu().numpy()
+    sums = [acc[j].astype(np.float32) for j in range(3)]
+    all_ = mean_iou(sums[0], sums[1], sums[2])
+    if category_split is None:
+        return all_, (sums[0], sums[1], sums[2])
+    base_i, novel_i = _split_indices(category_split, "base_category"), _split_indices(category_split, "novel_category")
+    base = mean_iou(sums[0][base_i], sums[1][base_i], sums[2][base_i])
+    novel = mean_iou(sums[0][novel_i], sums[1][novel_i], sums[2][novel_i])
+    iou_class = sums[0] / (sums[1] + np.float32(1e-10))
+    if logger:
+        logger.info("Val 2d result: mIoU_Base/mAcc_Base/allAcc_Base {:.4f}/{:.4f}/{:.4f}.".format(*base))
+        logger.info("Val 2d result: mIoU_Novel/mAcc_Novel/allAcc_Novel {:.4f}/{:.4f}/{:.4f}.".format(*novel))
+        logger.info("Val 2d result: mIoU_All/mAcc_All/allAcc_All {:.4f}/{:.4f}/{:.4f}.".format(*all_))
+    return ValidateResult(base, novel, all_, (iou_class[base_i], iou_class[novel_i], iou_class), tuple(acc))

@@ -721,6 +721,14 @@ def test_validate_matches_reference_run(gp, golden_dir, reference_scene):
     assert abs(float(np.mean(iou[gv["base"]])) - float(gv["miou_base"])) < 1e-7
     assert abs(float(np.mean(iou[gv["novel"]])) - float(gv["miou_novel"])) < 1e-7
     assert abs(miou - float(np.mean(iou))) < 1e-7
+    # the reference's own return value: (mIoU_Base, mIoU_Novel) from the Base / Novel / All meters (:458-553)
+    Replay.calls = 0
+    split = dict(base_category=gv["base"].tolist(), novel_category=gv["novel"].tolist())
+    r = validation.validate([batch_data, batch_data], Replay(), 20, [sc.ignore_label], category_split=split)
+    assert isinstance(r, tuple) and len(r) == 2
+    assert abs(r[0] - float(gv["miou_base"])) < 1e-7 and abs(r[1] - float(gv["miou_novel"])) < 1e-7, tuple(r)
+    assert r.all[0] == miou and r.sums[0].dtype == np.int64 and np.array_equal(r.sums[2], gv["target"].sum(0))
+    assert len(r.iou_class_base) == 12 and len(r.iou_class_novel) == 8
 
 
 # ----------------------------------------------------------------------------- F4 kNN on raw points
