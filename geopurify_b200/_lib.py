@@ -56,6 +56,7 @@ _SIGS = {
     "gp_voxelize": (c_int, [_P, c_int, c_int64, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
     "gp_voxel_index_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
     "gp_voxel_index_build": (c_int, [_P, c_int64, c_int, c_int, c_int, _P, _P, _P, c_size_t, _P]),
+    "gp_voxel_index_check": (c_int, [_P, c_int64, c_int, c_int, c_int, _P]),
     "gp_kernel_map": (c_int, [_P, c_int64, c_int, c_int, c_int, _P, _P]),
     "gp_knn_grid": (c_int, [_P, c_int64, c_int, c_int, c_int, c_int, _P, _P, _P]),
     "gp_knn_points_workspace_bytes": (c_size_t, [c_int64]),
@@ -114,14 +115,17 @@ def check(rc):
         raise GeoPurifyError(f"libgeopurify_b200 error {rc}: {msg}")
 
 
-def ptr(t):
-    """Device pointer of a CUDA tensor (None -> NULL).  Tensors must be contiguous."""
+def ptr(t, dtype=None):
+    """Device pointer of a CUDA tensor (None -> NULL).  Tensors must be contiguous; with `dtype` the element type
+    is checked too (the C ABI takes untyped pointers: an int64 tensor where int32 is expected would be reinterpreted)."""
     if t is None:
         return None
     if not t.is_cuda:
         raise GeoPurifyError("geopurify_b200 kernels need CUDA tensors (no CPU fallback)")
     if not t.is_contiguous():
         raise GeoPurifyError("tensor must be contiguous")
+    if dtype is not None and t.dtype != dtype:
+        raise GeoPurifyError(f"tensor dtype {t.dtype} where the C ABI expects {dtype}")
     return c_void_p(t.data_ptr())
 
 

@@ -66,9 +66,13 @@ class SonataXAffinityTrainer:
         self.logit_scale = float(logit_scale)
         self.view_features = view_features
         self.mask_features = mask_features
-        # "mean" = lift_lseg_features (A4), "consensus" = lift_xdecoder_features (A5, the reference's default teacher)
+        # "mean" = lift_lseg_features (A4), "consensus" = lift_xdecoder_features (A5, the reference's default teacher),
+        # "ape" = lift_ape_features (the APE teacher: the same consensus fusion on 256-d instance embeddings)
         self.lifting = lifting or ("consensus" if (mask_features is not None and view_features is None) else "mean")
+        if self.lifting not in ("mean", "consensus", "ape"):
+            raise ValueError(f"unknown lifting {self.lifting!r}")      # run/validation.py:106 raises ValueError too
         self.use_lseg = self.lifting == "mean"
+        self.use_ape = self.lifting == "ape"                           # models/affinity_module.py:1496-1497
         if K is not None:
             self.K = K
         if n_pool is not None:
@@ -125,8 +129,27 @@ class SonataXAffinityTrainer:
         (models/affinity_module.py:455-714 minus the X-Decoder forward and its mask post-processing).
         `self.mask_features(batch_data)` supplies (idmap [V,H,W] uint8, table [V,Q,D] float32) on the device: the
         panoptic-style partition of :544-570 and the kept queries' embeddings."""
-        scene_coords = batch_data[0]
         idmap, table = self.mask_features(batch_data)
+        return self._lift_masks(batch_data, idmap, table)
+
+    @torch.no_grad()
+    def lift_ape_features(self, batch_data):
+        """APE teacher variant (models/affinity_module.py:736-993), feature_dim = 256 (:763).  Per view a point takes
+        the MEAN of the embeddings of the final masks covering its pixel (:868-882); the final masks are the disjoint
+        arg-max partition of :844-858, so at most one mask covers a pixel and the mean is that mask's embedding (or
+        zero) -- the same gather as lift_xdecoder_features.  Per-view 1-NN fill (:895-911), normalise + logits
+        (:913-916), consensus top-min(3, #views) softmax fusion (:945-969) and the scene-level fill (:971-981) are
+        line for line those of the X-Decoder path, so both run through gp_lift_consensus.
+        `self.mask_features(batch_data)` supplies (idmap [V,H,W] uint8, table [V,Q,256] float32): the partition and
+        `outputs['scene_features_for_instances']` of the kept instances."""
+        idmap, table = self.mask_features(batch_data)
+        if table.shape[2] != self.feature_dim:
+            raise L.GeoPurifyError(f"lift_ape_features: embeddings are {table.shape[2]}-d, model feature_dim is "
+                                   f"{self.feature_dim} (the reference's APE path is 256-d)")
+        return self._lift_masks(batch_data, idmap, table)
+
+    def _lift_masks(self, batch_data, idmap, table):
+        scene_coords = batch_data[0]
         w, d = idmap.shape[2], table.shape[2]
         pix = self.pixels_from_batch(batch_data, w)
         xyz = scene_coords.float().cuda().contiguous()
@@ -169,13 +192,16 @@ class SonataXAffinityTrainer:
     def evaluate_scene(self, batch_data, vis_prefix="scene0695_00", keep_intermediates=False):
         """Reference signature and return value (models/affinity_module.py:1490-1608)."""
         if self.use_lseg:
-            f_full, text_features, logit_scale = self.lift_lseg_features(batch_data)      # :1498
+            f_full, text_features, logit_scale = self.lift_lseg_features(batch_data)      # :1495
+        elif self.use_ape:
+            f_full, text_features, logit_scale = self.lift_ape_features(batch_data)       # :1497
         else:
             f_full, text_features, logit_scale = self.lift_xdecoder_features(batch_data)  # :1500
         scene_coords_3d, inds = batch_data[1], batch_data[2]
         gauss = batch_data[19][:, :6].float().cuda().contiguous()
         vox = scene_coords_3d.to(torch.int32)
-        extent = tuple(int(e) + 1 for e in vox.max(0).values.tolist())
+        vox = vox - vox.min(0).values          # any integer origin (MinkowskiEngine-style negative coordinates too):
+        extent = tuple(int(e) + 1 for e in vox.max(0).values.tolist())   # kernel map and kNN are translation invariant
         if keep_intermediates:
             self.last_lifted = f_full
         pooled, p2v_sorted = self.purify(f_full, gauss, vox.cuda().contiguous(), inds.to(torch.int32).cuda(), extent,
@@ -194,7 +220,7 @@ class SonataXAffinityTrainer:
         pix, counts = ops.project_views(s.coords, s.w2c, s.intr, s.depth, H, W, s.cut, s.vis_thres)
         keep = ops.accept_views(counts, self.min_visible)
         self._mark("project")
-        if self.lifting == "consensus":
+        if self.lifting in ("consensus", "ape"):
             lifted, seen = ops.lift_consensus(pix, keep, s.idmaps, s.tables, self.text_features, self.logit_scale,
                                               s.coords_f32, self.fill_cell)
         elif s.feat is None:      # compact 2-D form only: gather through the id map, no dense map

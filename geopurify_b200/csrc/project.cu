@@ -20,6 +20,26 @@ __device__ __forceinline__ void load_cams(Cam* s, const double* w2c, const doubl
   }
 }
 
+// Field-major copy for kernels whose LANES walk the views (lift_mean_kernel): s[j * nv + v].  With the 128-byte Cam
+// records above, lane = view puts all 32 lanes on the same two banks (a 32-way conflict on each of the 16 loads of a
+// projection); field-major, consecutive lanes read consecutive doubles.
+__device__ __forceinline__ void load_cams_soa(double* s, const double* w2c, const double* intr, int nv) {
+  for (int i = threadIdx.x; i < nv * 16; i += blockDim.x) {
+    int v = i >> 4, j = i & 15;
+    s[j * nv + v] = j < 12 ? w2c[(size_t)v * 16 + j] : intr[(size_t)v * 4 + (j - 12)];
+  }
+}
+__device__ __forceinline__ Cam cam_from_soa(const double* s, int nv, int v) {
+  Cam c;
+#pragma unroll
+  for (int j = 0; j < 12; ++j) c.m[j] = s[j * nv + v];
+  c.fx = s[12 * nv + v];
+  c.fy = s[13 * nv + v];
+  c.cx = s[14 * nv + v];
+  c.cy = s[15 * nv + v];
+  return c;
+}
+
 // numpy's 4x4 @ 4xN float64 product runs through OpenBLAS dgemm: an FMA chain over k = 0..3 starting from
 // a0*x (verified bit-for-bit against numpy); the rest is separate IEEE ops (numpy ufuncs).
 __device__ __forceinline__ bool project_point(const Cam& c, double x, double y, double z, int H, int W, int cut,
@@ -225,39 +245,53 @@ extern "C" int gp_accept_views(const int32_t* counts, int V, int min_visible, in
 }
 
 // ------------------------------------------------------------------ fused lifting
-// One warp per point.  Lane l projects views l, l+32, ... (cameras in shared memory), the warp ballots the
-// visible set and then walks it in ascending view order, every lane pulling 128-bit pieces of the feature row.
+// One warp per point.  Lane l projects views l, l+32 of a 64-view chunk (cameras in shared memory; the two depth
+// samples of a lane are independent loads), the warp ballots the visible set and then walks it in ascending view
+// order in BATCHES of up to RB rows: all RB feature rows are requested before the first is added, so a lane has
+// RB x (row bytes / 512) independent 128-bit loads in flight instead of one row's worth (round 1: 28 % of HBM peak,
+// latency-bound on the depth -> pixel-row chain).  The adds stay in view order: the sum is bit-identical.
 // NV4 = float4 accumulators per lane: D = 128 * NV4.
 template <int NV4, bool BF16>
-__device__ __forceinline__ void accumulate_row(const void* feat, size_t row_index, int D, int lane, float4 (&acc)[NV4]) {
+struct RowRegs {
+  static constexpr int NL = BF16 ? (NV4 / 2 > 0 ? NV4 / 2 : 1) : NV4;   // 128-bit loads per lane per row
+  uint4 t[NL];
+};
+
+template <int NV4, bool BF16>
+__device__ __forceinline__ void load_row(const void* feat, size_t row_index, int D, int lane, RowRegs<NV4, BF16>& r) {
   if constexpr (!BF16) {
-    const float4* p = (const float4*)((const float*)feat + row_index * (size_t)D);
-    float4 t[NV4];
+    const uint4* p = (const uint4*)((const float*)feat + row_index * (size_t)D);
 #pragma unroll
-    for (int j = 0; j < NV4; ++j) t[j] = ldg_stream_f4(p + j * 32 + lane);
-#pragma unroll
-    for (int j = 0; j < NV4; ++j) {
-      acc[j].x = __fadd_rn(acc[j].x, t[j].x);
-      acc[j].y = __fadd_rn(acc[j].y, t[j].y);
-      acc[j].z = __fadd_rn(acc[j].z, t[j].z);
-      acc[j].w = __fadd_rn(acc[j].w, t[j].w);
-    }
+    for (int j = 0; j < NV4; ++j) r.t[j] = ldg_stream_u4(p + j * 32 + lane);
   } else {
     // lane owns 8 consecutive bf16 per 256-element chunk -> two float4 accumulators per uint4
     const uint4* p = (const uint4*)((const __nv_bfloat16*)feat + row_index * (size_t)D);
-    uint4 t[NV4 / 2 > 0 ? NV4 / 2 : 1];
 #pragma unroll
-    for (int j = 0; j < NV4 / 2; ++j) t[j] = ldg_stream_u4(p + j * 32 + lane);
+    for (int j = 0; j < NV4 / 2; ++j) r.t[j] = ldg_stream_u4(p + j * 32 + lane);
+  }
+}
+
+template <int NV4, bool BF16>
+__device__ __forceinline__ void add_row(const RowRegs<NV4, BF16>& r, float4 (&acc)[NV4]) {
+  if constexpr (!BF16) {
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) {
+      acc[j].x = __fadd_rn(acc[j].x, __uint_as_float(r.t[j].x));
+      acc[j].y = __fadd_rn(acc[j].y, __uint_as_float(r.t[j].y));
+      acc[j].z = __fadd_rn(acc[j].z, __uint_as_float(r.t[j].z));
+      acc[j].w = __fadd_rn(acc[j].w, __uint_as_float(r.t[j].w));
+    }
+  } else {
 #pragma unroll
     for (int j = 0; j < NV4 / 2; ++j) {
-      acc[2 * j].x = __fadd_rn(acc[2 * j].x, __uint_as_float(t[j].x << 16));
-      acc[2 * j].y = __fadd_rn(acc[2 * j].y, __uint_as_float(t[j].x & 0xffff0000u));
-      acc[2 * j].z = __fadd_rn(acc[2 * j].z, __uint_as_float(t[j].y << 16));
-      acc[2 * j].w = __fadd_rn(acc[2 * j].w, __uint_as_float(t[j].y & 0xffff0000u));
-      acc[2 * j + 1].x = __fadd_rn(acc[2 * j + 1].x, __uint_as_float(t[j].z << 16));
-      acc[2 * j + 1].y = __fadd_rn(acc[2 * j + 1].y, __uint_as_float(t[j].z & 0xffff0000u));
-      acc[2 * j + 1].z = __fadd_rn(acc[2 * j + 1].z, __uint_as_float(t[j].w << 16));
-      acc[2 * j + 1].w = __fadd_rn(acc[2 * j + 1].w, __uint_as_float(t[j].w & 0xffff0000u));
+      acc[2 * j].x = __fadd_rn(acc[2 * j].x, __uint_as_float(r.t[j].x << 16));
+      acc[2 * j].y = __fadd_rn(acc[2 * j].y, __uint_as_float(r.t[j].x & 0xffff0000u));
+      acc[2 * j].z = __fadd_rn(acc[2 * j].z, __uint_as_float(r.t[j].y << 16));
+      acc[2 * j].w = __fadd_rn(acc[2 * j].w, __uint_as_float(r.t[j].y & 0xffff0000u));
+      acc[2 * j + 1].x = __fadd_rn(acc[2 * j + 1].x, __uint_as_float(r.t[j].z << 16));
+      acc[2 * j + 1].y = __fadd_rn(acc[2 * j + 1].y, __uint_as_float(r.t[j].z & 0xffff0000u));
+      acc[2 * j + 1].z = __fadd_rn(acc[2 * j + 1].z, __uint_as_float(r.t[j].w << 16));
+      acc[2 * j + 1].w = __fadd_rn(acc[2 * j + 1].w, __uint_as_float(r.t[j].w & 0xffff0000u));
     }
   }
 }
@@ -289,25 +323,28 @@ __device__ __forceinline__ void store_mean(float* out, int64_t out_stride, int64
 }
 
 template <typename CT, int DEPTH_DTYPE, int NV4, bool BF16, bool FROM_PIX>
-__global__ void __launch_bounds__(256) lift_mean_kernel(const void* __restrict__ coords, int64_t n,
-                                                         const double* __restrict__ w2c,
-                                                         const double* __restrict__ intr,
-                                                         const void* __restrict__ depth, int V, int H, int W, int cut,
-                                                         double thr, const uint8_t* __restrict__ keep,
-                                                         const int32_t* __restrict__ pix_in,
-                                                         const void* __restrict__ feat, int D, float* __restrict__ out,
-                                                         int64_t out_stride, uint8_t* __restrict__ seen,
-                                                         const uint8_t* __restrict__ idmap, int Q) {
+__global__ void __launch_bounds__(128, 5) lift_mean_kernel(const void* __restrict__ coords, int64_t n,
+                                                            const double* __restrict__ w2c,
+                                                            const double* __restrict__ intr,
+                                                            const void* __restrict__ depth, int V, int H, int W, int cut,
+                                                            double thr, const uint8_t* __restrict__ keep,
+                                                            const int32_t* __restrict__ pix_in,
+                                                            const void* __restrict__ feat, int D, float* __restrict__ out,
+                                                            int64_t out_stride, uint8_t* __restrict__ seen,
+                                                            const uint8_t* __restrict__ idmap, int Q) {
   extern __shared__ double smem_d[];
-  Cam* cams = (Cam*)smem_d;
-  uint8_t* skeep = (uint8_t*)(cams + (FROM_PIX ? 0 : V));
-  if (!FROM_PIX) load_cams(cams, w2c, intr, 0, V);
+  double* cams = smem_d;   // field-major: cams[j * V + v]
+  uint8_t* skeep = (uint8_t*)(cams + (FROM_PIX ? 0 : 16 * V));
+  if (!FROM_PIX) load_cams_soa(cams, w2c, intr, V);
   for (int i = threadIdx.x; i < V; i += blockDim.x) skeep[i] = keep ? keep[i] : 1;
   __syncthreads();
   const float thr32 = (float)thr;
   const int lane = threadIdx.x & 31;
   const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
   const size_t hw = (size_t)H * W;
+  // rows in flight per batch: 32 registers' worth of 128-bit loads per lane (bf16 D = 512: 4 rows x 2 loads)
+  constexpr int NL = RowRegs<NV4, BF16>::NL;
+  constexpr int RB = 8 / NL > 4 ? 4 : (8 / NL < 1 ? 1 : 8 / NL);
   for (int64_t i = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < n; i += warps_total) {
     double x = 0, y = 0, z = 0;
     if (!FROM_PIX) load_xyz<CT>(coords, i, x, y, z);
@@ -315,30 +352,54 @@ __global__ void __launch_bounds__(256) lift_mean_kernel(const void* __restrict__
 #pragma unroll
     for (int j = 0; j < NV4; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
     int count = 0;
-    for (int v0 = 0; v0 < V; v0 += 32) {
-      int v = v0 + lane;
-      int p = -1;
-      if (v < V && skeep[v]) {
-        if (FROM_PIX) {
-          p = __ldg(pix_in + (size_t)v * n + i);
-        } else {
-          int row, col;
-          double pz;
-          if (project_point(cams[v], x, y, z, H, W, cut, pz, row, col) &&
-              depth_test<DEPTH_DTYPE>(depth, (size_t)v * hw + (size_t)row * W + col, pz, thr, thr32))
-            p = row * W + col;
+    for (int v0 = 0; v0 < V; v0 += 64) {
+      // ---- which of the chunk's 64 views see the point, and which feature row each one reads
+      int p[2];
+      uint32_t ri[2];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int v = v0 + 32 * h + lane;
+        p[h] = -1;
+        if (v < V && skeep[v]) {
+          if (FROM_PIX) {
+            p[h] = __ldg(pix_in + (size_t)v * n + i);
+          } else {
+            int row, col;
+            double pz;
+            if (project_point(cam_from_soa(cams, V, v), x, y, z, H, W, cut, pz, row, col) &&
+                depth_test<DEPTH_DTYPE>(depth, (size_t)v * hw + (size_t)row * W + col, pz, thr, thr32))
+              p[h] = row * W + col;
+          }
         }
       }
-      unsigned b = __ballot_sync(0xffffffffu, p >= 0);
-      count += __popc(b);
-      // compact 2-D form: the pixel's row is table[v, idmap[v, pixel]] instead of feat[v, pixel]
-      size_t ri = 0;
-      if (p >= 0) ri = idmap ? (size_t)v * Q + min((int)__ldg(idmap + (size_t)v * hw + p), Q - 1) : (size_t)v * hw + (size_t)p;
-      while (b) {
-        int src = __ffs(b) - 1;
-        b &= b - 1;
-        unsigned long long rr = __shfl_sync(0xffffffffu, (unsigned long long)ri, src);
-        accumulate_row<NV4, BF16>(feat, (size_t)rr, D, lane, acc);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int v = v0 + 32 * h + lane;
+        // compact 2-D form: the pixel's row is table[v, idmap[v, pixel]] instead of feat[v, pixel]
+        ri[h] = 0;
+        if (p[h] >= 0)
+          ri[h] = idmap ? (uint32_t)(v * Q + min((int)__ldg(idmap + (size_t)v * hw + p[h]), Q - 1))
+                        : (uint32_t)((size_t)v * hw + (size_t)p[h]);
+      }
+      unsigned long long mask = (unsigned long long)__ballot_sync(0xffffffffu, p[0] >= 0) |
+                                ((unsigned long long)__ballot_sync(0xffffffffu, p[1] >= 0) << 32);
+      count += __popcll(mask);
+      // ---- ascending view order, RB rows in flight per batch
+      while (mask) {
+        RowRegs<NV4, BF16> rows[RB];
+        bool ok[RB];
+#pragma unroll
+        for (int k = 0; k < RB; ++k) {
+          ok[k] = mask != 0;
+          const int src = ok[k] ? __ffsll((long long)mask) - 1 : 0;
+          if (ok[k]) mask &= mask - 1;
+          const uint32_t a = __shfl_sync(0xffffffffu, ri[0], src & 31);
+          const uint32_t b2 = __shfl_sync(0xffffffffu, ri[1], src & 31);
+          if (ok[k]) load_row<NV4, BF16>(feat, (size_t)(src < 32 ? a : b2), D, lane, rows[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < RB; ++k)
+          if (ok[k]) add_row<NV4, BF16>(rows[k], acc);
       }
     }
     store_mean<NV4, BF16>(out, out_stride, i, lane, acc, count);
@@ -353,12 +414,12 @@ static int launch_lift(const void* coords, int64_t n, const double* w2c, const d
                        const uint8_t* idmap = nullptr, int Q = 0) {
   size_t smem = (FROM_PIX ? 0 : sizeof(Cam) * V) + V;
   int64_t warps = n;
-  int64_t blocks = (warps + 7) / 8;
-  int64_t cap = (int64_t)GP_SM_COUNT * 8 * 16;  // grid-stride beyond 16 waves of 8 CTAs/SM
+  int64_t blocks = (warps + 3) / 4;
+  int64_t cap = (int64_t)GP_SM_COUNT * 5 * 16;  // grid-stride beyond 16 waves of 5 CTAs (4 warps, ~96 registers) per SM
   unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
   int nv4 = D / 128;
 #define LIFT(NV4, BF)                                                                                        \
-  lift_mean_kernel<CT, DD, NV4, BF, FROM_PIX><<<grid, 256, smem, st>>>(coords, n, w2c, intr, depth, V, H, W, \
+  lift_mean_kernel<CT, DD, NV4, BF, FROM_PIX><<<grid, 128, smem, st>>>(coords, n, w2c, intr, depth, V, H, W, \
                                                                        cut, thr, keep, pix, feat, D, out,    \
                                                                        out_stride, seen, idmap, Q)
   if (feat_dtype == GP_F32) {

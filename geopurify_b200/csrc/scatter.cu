@@ -45,6 +45,8 @@ __global__ void scatter_offsets_kernel(const uint32_t* __restrict__ keys_sorted,
   if (s > n) return;
   int64_t prev = s == 0 ? -1 : (int64_t)keys_sorted[s - 1];
   int64_t cur = s == n ? m : (int64_t)keys_sorted[s];
+  if (prev > m) prev = m;   // an out-of-range destination row (caller error) must not write past offsets[m]
+  if (cur > m) cur = m;
   for (int64_t v = prev + 1; v <= cur; ++v) offsets[v] = (int32_t)s;
 }
 

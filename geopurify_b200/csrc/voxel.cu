@@ -11,7 +11,7 @@ struct VoxelIndexLayout {
   int cx, cy, cz;
   int64_t ncell;
   int key_bits;
-  size_t off_sorted, off_cells, off_rank, off_keys_in, off_keys_out, off_vals_in, off_vals_out, off_cub;
+  size_t off_sorted, off_cells, off_rank, off_keys_in, off_keys_out, off_vals_in, off_vals_out, off_cub, off_status;
   size_t cub_bytes, total;
 };
 
@@ -48,6 +48,7 @@ static bool voxel_index_layout(int64_t m, int ex, int ey, int ez, VoxelIndexLayo
   cub::DeviceRadixSort::SortPairs(nullptr, L.cub_bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
                                   (const int32_t*)nullptr, (int32_t*)nullptr, (int)m, 0, L.key_bits);
   L.off_cub = take(L.cub_bytes + 256);
+  L.off_status = take(sizeof(int32_t));   // != 0: a voxel coordinate was outside [0, extent)
   L.total = off;
   return true;
 }
@@ -111,7 +112,8 @@ __global__ void index_finalize_kernel(const int32_t* __restrict__ vox, const uin
                                       const int32_t* __restrict__ vals_sorted, int64_t m, int cx, int cy,
                                       int4* __restrict__ sorted, int2* __restrict__ cells,
                                       int32_t* __restrict__ rank_ws, int32_t* __restrict__ order,
-                                      int32_t* __restrict__ rank) {
+                                      int32_t* __restrict__ rank, int ex, int ey, int ez,
+                                      int32_t* __restrict__ status) {
   int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= m) return;
   int orig = vals_sorted[s];
@@ -120,6 +122,10 @@ __global__ void index_finalize_kernel(const int32_t* __restrict__ vox, const uin
   rank_ws[orig] = (int32_t)s;
   if (order) order[s] = orig;
   if (rank) rank[orig] = (int32_t)s;
+  if (x < 0 || y < 0 || z < 0 || x >= ex || y >= ey || z >= ez) {  // caller error: no cell-table write, flag it
+    atomicOr(status, 1);
+    return;
+  }
   uint64_t ck = keys_sorted[s] >> (3 * GP_CELL_SHIFT);
   int64_t lin = ((int64_t)(z >> GP_CELL_SHIFT) * cy + (y >> GP_CELL_SHIFT)) * cx + (x >> GP_CELL_SHIFT);
   if (s == 0 || (keys_sorted[s - 1] >> (3 * GP_CELL_SHIFT)) != ck) cells[lin].x = (int)s;
@@ -145,6 +151,7 @@ extern "C" int gp_voxel_index_build(const int32_t* vox, int64_t m, int ex, int e
   cudaStream_t st = (cudaStream_t)stream;
   char* ws = (char*)workspace;
   GP_CUDA(cudaMemsetAsync(ws + L.off_cells, 0, sizeof(int2) * (size_t)L.ncell, st));
+  GP_CUDA(cudaMemsetAsync(ws + L.off_status, 0, sizeof(int32_t), st));
   if (m == 0) return GP_OK;
   uint64_t* kin = (uint64_t*)(ws + L.off_keys_in);
   uint64_t* kout = (uint64_t*)(ws + L.off_keys_out);
@@ -156,8 +163,24 @@ extern "C" int gp_voxel_index_build(const int32_t* vox, int64_t m, int ex, int e
   size_t cb = L.cub_bytes + 256;
   GP_CUDA(cub::DeviceRadixSort::SortPairs(ws + L.off_cub, cb, kin, kout, vin, vout, (int)m, 0, L.key_bits, st));
   index_finalize_kernel<<<grid, 256, 0, st>>>(vox, kout, vout, m, L.cx, L.cy, (int4*)(ws + L.off_sorted),
-                                              (int2*)(ws + L.off_cells), (int32_t*)(ws + L.off_rank), order, rank);
+                                              (int2*)(ws + L.off_cells), (int32_t*)(ws + L.off_rank), order, rank,
+                                              ex, ey, ez, (int32_t*)(ws + L.off_status));
   GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+// Synchronising check of a built index: GP_ERR_ARG if any voxel coordinate was outside [0, extent) (such voxels are
+// kept out of the cell table, so nothing was written out of bounds, but kernel map / kNN results are meaningless).
+extern "C" int gp_voxel_index_check(const void* index_workspace, int64_t m, int ex, int ey, int ez,
+                                    gp_stream_t stream) {
+  VoxelIndexLayout L;
+  GP_CHECK_ARG(voxel_index_layout(m, ex, ey, ez, L), "gp_voxel_index_check: bad sizes");
+  int32_t flag = 0;
+  GP_CUDA(cudaMemcpyAsync(&flag, (const char*)index_workspace + L.off_status, sizeof(flag), cudaMemcpyDeviceToHost,
+                          (cudaStream_t)stream));
+  GP_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  GP_CHECK_ARG(flag == 0, "voxel index: a voxel coordinate lies outside [0, extent) = [0,%d) x [0,%d) x [0,%d) "
+               "(shift the coordinates by their minimum and pass extent = max + 1)", ex, ey, ez);
   return GP_OK;
 }
 

@@ -246,9 +246,15 @@ class VoxelIndex:
         self.ws = _ws(nb)
         self.order = torch.empty((self.m,), dtype=torch.int32, device=_dev())
         self.rank = torch.empty((self.m,), dtype=torch.int32, device=_dev())
-        L.check(lib.gp_voxel_index_build(L.ptr(vox_i32), self.m, self.ex, self.ey, self.ez, L.ptr(self.order),
-                                         L.ptr(self.rank), L.ptr(self.ws), nb, L.stream()))
+        L.check(lib.gp_voxel_index_build(L.ptr(vox_i32, torch.int32), self.m, self.ex, self.ey, self.ez,
+                                         L.ptr(self.order), L.ptr(self.rank), L.ptr(self.ws), nb, L.stream()))
         L.count(8)
+
+    def check(self):
+        """Synchronising validity check: raises if a voxel coordinate was outside [0, extent) (the build never writes
+        out of bounds for such input, but kernel map and kNN would be meaningless)."""
+        L.check(L.load().gp_voxel_index_check(L.ptr(self.ws), self.m, self.ex, self.ey, self.ez, L.stream()))
+        return self
 
     def kernel_map(self):
         lib = L.load()
@@ -305,7 +311,7 @@ class ScatterPlan:
         self.n, self.m = p2v_i32.shape[0], int(m)
         nb = lib.gp_scatter_mean_workspace_bytes(self.n, self.m)
         self.ws = _ws(nb)
-        L.check(lib.gp_scatter_mean_prepare(L.ptr(p2v_i32), self.n, self.m, L.ptr(self.ws), nb, L.stream()))
+        L.check(lib.gp_scatter_mean_prepare(L.ptr(p2v_i32, torch.int32), self.n, self.m, L.ptr(self.ws), nb, L.stream()))
         L.count(6)
 
     def mean(self, src, D, out, col0=0):
@@ -320,7 +326,8 @@ def affinity_softmax(embed, nbr_sorted, sharpen=20.0):
     lib = L.load()
     m, k = nbr_sorted.shape
     w = torch.empty((m, k), dtype=torch.float32, device=_dev())
-    L.check(lib.gp_affinity_softmax(L.ptr(embed), embed.shape[1], L.ptr(nbr_sorted), m, k, float(sharpen), L.ptr(w),
+    L.check(lib.gp_affinity_softmax(L.ptr(embed, torch.float32), embed.shape[1], L.ptr(nbr_sorted, torch.int32), m, k,
+                                    float(sharpen), L.ptr(w),
                                     L.stream()))
     L.count(1)
     return w
@@ -341,7 +348,8 @@ def pool(f0, D, nbr_sorted, weights, T, tensor_core=None):
     if tensor_core:
         nbp = lib.gp_pool_plan_bytes(m, k)
         plan = _ws(nbp)
-        L.check(lib.gp_pool_plan(L.ptr(nbr_sorted), L.ptr(weights), m, k, L.ptr(plan), nbp, L.stream()))
+        L.check(lib.gp_pool_plan(L.ptr(nbr_sorted, torch.int32), L.ptr(weights, torch.float32), m, k, L.ptr(plan), nbp,
+                                 L.stream()))
         nbw = lib.gp_pool_tc_workspace_bytes(m)
         ws = _ws(nbw)
         out = torch.empty((m, D), dtype=torch.float32, device=_dev())
@@ -352,7 +360,8 @@ def pool(f0, D, nbr_sorted, weights, T, tensor_core=None):
     a = torch.empty((m, D), dtype=torch.float32, device=_dev())
     b = torch.empty((m, D), dtype=torch.float32, device=_dev()) if T > 1 else a
     outp = ctypes.c_void_p()
-    L.check(lib.gp_pool(L.ptr(f0), f0.stride(0), D, L.ptr(nbr_sorted), L.ptr(weights), m, k, T, L.ptr(a), L.ptr(b),
+    L.check(lib.gp_pool(L.ptr(f0, torch.float32), f0.stride(0), D, L.ptr(nbr_sorted, torch.int32),
+                        L.ptr(weights, torch.float32), m, k, T, L.ptr(a), L.ptr(b),
                         ctypes.byref(outp), L.stream()))
     L.count(T)
     return a if outp.value == a.data_ptr() else b
@@ -362,7 +371,8 @@ def gather_rows(rows, D, index_i32):
     lib = L.load()
     n = index_i32.shape[0]
     out = torch.empty((n, D), dtype=torch.float32, device=_dev())
-    L.check(lib.gp_gather_rows(L.ptr(rows), rows.stride(0), D, L.ptr(index_i32), n, L.ptr(out), L.stream()))
+    L.check(lib.gp_gather_rows(L.ptr(rows, torch.float32), rows.stride(0), D, L.ptr(index_i32, torch.int32), n,
+                               L.ptr(out), L.stream()))
     L.count(1)
     return out
 
@@ -397,8 +407,11 @@ def iou_hist(label_rows, index, target, ignore, C, hist=None, want_pred=False):
     n = target.shape[0]
     if hist is None:
         hist = torch.zeros((3, C), dtype=torch.int64, device=_dev())
+    if ignore is None:       # no ignore ids
+        ignore = torch.empty((0,), dtype=torch.int64, device=_dev())
     pred = torch.empty((n,), dtype=torch.int64, device=_dev()) if want_pred else None
-    L.check(lib.gp_iou_hist(L.ptr(label_rows), L.ptr(index), L.ptr(target), n, L.ptr(ignore), ignore.shape[0], C,
-                            L.ptr(pred), L.ptr(hist), L.stream()))
+    L.check(lib.gp_iou_hist(L.ptr(label_rows, torch.int32), L.ptr(index, torch.int32), L.ptr(target, torch.int64), n,
+                            L.ptr(ignore, torch.int64), ignore.shape[0], C, L.ptr(pred), L.ptr(hist, torch.int64),
+                            L.stream()))
     L.count(1)
     return hist, pred

@@ -173,6 +173,9 @@ int gp_voxelize(const void* coords, int coords_dtype, int64_t n, const double* x
 size_t gp_voxel_index_workspace_bytes(int64_t m, int ex, int ey, int ez);
 int gp_voxel_index_build(const int32_t* vox, int64_t m, int ex, int ey, int ez, int32_t* order, int32_t* rank,
                          void* workspace, size_t workspace_bytes, gp_stream_t stream);
+/* Synchronising validity check of a built index: GP_ERR_ARG if a voxel coordinate was outside [0, extent).  The build
+ * itself never writes out of bounds for such input (the voxel is left out of the cell table and a flag is raised). */
+int gp_voxel_index_check(const void* index_workspace, int64_t m, int ex, int ey, int ez, gp_stream_t stream);
 
 /* ---- A7: 3^3 kernel map in SORTED space: nbr27[s, o] = sorted position of the voxel at coord(s) + delta_o,
  * o = (dx+1) + 3(dy+1) + 9(dz+1), or -1. */

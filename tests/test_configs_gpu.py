@@ -94,9 +94,64 @@ def test_reference_tuple_surface_consensus_and_mean(small_state):
     assert mean_model.use_lseg and not cons_model.use_lseg
     r_mean = mean_model.evaluate_scene(tuple(batch))
     r_cons = cons_model.evaluate_scene(tuple(batch))
+    # any integer voxel origin (ME-style negative coordinates): same features, nothing out of bounds
+    shifted = list(batch)
+    shifted[1] = batch[1] - 37.0
+    assert torch.equal(mean_model.evaluate_scene(tuple(shifted))["scene_features"], r_mean["scene_features"])
     ref = oracle.evaluate_scene(sc, small_state, k=16, n_iter=3, min_visible=50)
     assert set(r_mean) == {"scene_features", "text_features", "logit_scale"}
     assert r_mean["scene_features"].shape == (n, 128) and r_cons["scene_features"].shape == (n, 128)
     assert (r_mean["scene_features"].cpu() - ref["scene_features"]).abs().max().item() < 1e-3
     # consensus lifting gives different (but finite, non-degenerate) features on the same surface
     assert torch.isfinite(r_cons["scene_features"]).all() and r_cons["scene_features"].abs().sum() > 0
+
+
+def test_ape_variant_d256_tuple_api_matches_oracle():
+    """`lift_ape_features` (models/affinity_module.py:736-993; selected at :1497): the consensus fusion on 256-d
+    instance embeddings, then the whole purification at D = 256 (student 262 -> ..., tcgen05 pooling in its one-pass
+    256-column form) through the reference's tuple surface, against the oracle's restatement of the same lines."""
+    from geopurify_b200.affinity_module import SonataXAffinityTrainer
+    from geopurify_b200.student import AffinityPredictor, load_numpy_state
+    from oracle import oracle
+    sc = synth.make_scene(n_points=9000, n_views=5, image_dim=(80, 60), seed=13, room=(2.0, 1.6, 2.0), n_boxes=2,
+                          cut=2, q_range=(4, 12), feat_dim=256, n_classes=7)
+    state = synth.make_student_state(input_dim=262, hidden_dim=128, embed_dim=128, seed=13)
+    W, H = sc.image_dim
+    kmap = oracle.mapper_intrinsics(sc.intrinsics, sc.image_dim)
+    maps = np.stack([oracle.project_view(sc.w2c[v].T.copy(), sc.coords.astype(np.float64), sc.depth[v], kmap, (W, H),
+                                         sc.vis_thres, sc.cut)[0] for v in range(sc.n_views)])
+    kept, rows, cols, pids = oracle.accept_views(maps, 50)
+    n = sc.n_points
+    batch = [None] * 20
+    batch[0] = torch.as_tensor(sc.coords)
+    batch[1] = torch.as_tensor(sc.voxel_coords).float()
+    batch[2] = torch.as_tensor(sc.inds_reconstruct)
+    batch[3] = torch.as_tensor(sc.labels)
+    batch[12] = torch.cat([torch.as_tensor(r) for r in rows])
+    batch[13] = torch.cat([torch.as_tensor(c) for c in cols])
+    batch[14] = torch.cat([torch.stack([torch.full((n,), i), torch.as_tensor(maps[v][:, 2])], 1)
+                           for i, v in enumerate(kept)])
+    batch[19] = torch.as_tensor(sc.gauss)
+    idm = torch.as_tensor(sc.idmaps[kept]).cuda()
+    tab = torch.as_tensor(sc.tables[kept]).cuda()
+    model = SonataXAffinityTrainer(mask_features=lambda b: (idm, tab), lifting="ape", text_features=sc.text,
+                                   logit_scale=sc.logit_scale, feature_dim=256, K=16, n_pool=3,
+                                   student=load_numpy_state(AffinityPredictor(262, 128, 128), state))
+    assert model.use_ape and not model.use_lseg
+    got = model.evaluate_scene(tuple(batch), keep_intermediates=True)
+    assert got["scene_features"].shape == (n, 256)
+
+    vpf = [sc.tables[v][sc.idmaps[v][rows[i], cols[i]].astype(np.int64)] for i, v in enumerate(kept)]
+    lifted, seen = oracle.lift_consensus(n, sc.coords, vpf, pids, sc.text, sc.logit_scale, 256)
+    assert (model.last_lifted.cpu() - lifted).abs().max().item() < 1e-5
+    vin = torch.cat([oracle.scatter_mean(lifted, sc.inds_reconstruct),
+                     oracle.scatter_mean(sc.gauss[:, :6], sc.inds_reconstruct)], 1)
+    emb = oracle.student_forward(vin, sc.voxel_coords, state)
+    nbr = oracle.knn_c(sc.voxel_coords, 16)
+    w = oracle.affinity_weights(emb, nbr, 20.0)
+    want = oracle.pool(vin, nbr, w, 3)[torch.as_tensor(sc.inds_reconstruct)][:, :256]
+    err = (got["scene_features"].cpu() - want).abs().max().item()
+    print(f"APE variant D=256: scene features max-abs {err:.2e}")
+    assert err < 1e-3
+    with pytest.raises(ValueError):
+        SonataXAffinityTrainer(text_features=sc.text, lifting="nope")

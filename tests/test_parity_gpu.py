@@ -842,3 +842,29 @@ def test_mine_contrastive_matches_reference_run(gp, golden_dir):
         if loc[15] - loc[14] > 1e-4:
             assert set(neg[r, 48:].tolist()) == set(g["negatives"][r, 48:].tolist())
     assert checked > a // 2
+
+
+# ----------------------------------------------------------------------------- caller errors fail loudly
+def test_out_of_range_inputs_are_flagged_not_written_out_of_bounds(gp):
+    from geopurify_b200 import _lib
+    vox = torch.tensor([[0, 0, 0], [1, 2, 3], [-1, 0, 0], [2, 2, 9]], dtype=torch.int32, device="cuda")
+    idx = gp.VoxelIndex(vox, extent=(4, 4, 4))            # two voxels outside [0,4)^3
+    with pytest.raises(_lib.GeoPurifyError, match="outside"):
+        idx.check()
+    gp.VoxelIndex(vox[:2].contiguous(), extent=(4, 4, 4)).check()
+    with pytest.raises(_lib.GeoPurifyError, match="dtype"):
+        gp.VoxelIndex(vox.long(), extent=(4, 4, 4))          # int64 where the C ABI expects int32
+    with pytest.raises(_lib.GeoPurifyError, match="dtype"):
+        gp.ScatterPlan(torch.zeros(5, dtype=torch.int64, device="cuda"), 3)
+    # destination rows beyond m: clamped inside the offsets table (no out-of-bounds write), valid rows unaffected
+    p2v = torch.tensor([0, 1, 7, 1], dtype=torch.int32, device="cuda")
+    plan = gp.ScatterPlan(p2v, 2)
+    src = torch.arange(8, dtype=torch.float32, device="cuda").view(4, 2).contiguous()
+    out = torch.zeros((2, 4), dtype=torch.float32, device="cuda")
+    plan.mean(src, 2, out, 0)
+    assert out[0, :2].tolist() == [0.0, 1.0] and out[1, :2].tolist() == [4.0, 5.0]
+    # histograms without ignore ids
+    lab = torch.tensor([0, 1, 1], dtype=torch.int32, device="cuda")
+    tgt = torch.tensor([0, 1, 0], dtype=torch.int64, device="cuda")
+    hist, _ = gp.iou_hist(lab, None, tgt, None, 2)
+    assert hist.cpu().tolist() == [[1, 1], [2, 2], [2, 1]]
