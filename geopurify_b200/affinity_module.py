@@ -170,7 +170,9 @@ class SonataXAffinityTrainer:
         p2v_sorted = index.rank[p2v_i32.long()].contiguous()
         plan = ops.ScatterPlan(p2v_sorted, m)
         stride = self.affinity_student.input_stride
-        vin = torch.zeros((m, stride), dtype=torch.float32, device=lifted.device)
+        vin = torch.empty((m, stride), dtype=torch.float32, device=lifted.device)
+        if stride > d + 6:
+            vin[:, d + 6:].zero_()       # only the pad columns: the two scatter-means write every other element
         plan.mean(lifted, d, vin, 0)
         plan.mean(gauss, 6, vin, d)
         self._mark("voxel_mean")

@@ -5,6 +5,7 @@ Every function enqueues on the current CUDA stream and returns device tensors.
 from __future__ import annotations
 
 import ctypes
+import os
 
 import numpy as np
 import torch
@@ -16,8 +17,44 @@ def _dev():
     return torch.device("cuda", torch.cuda.current_device())
 
 
+# Guard bands around every workspace (GEOPURIFY_B200_GUARD=1, or guard_workspaces(True)): compute-sanitizer is closed on
+# the build pool, so out-of-bounds writes of the kernels' internal indexing (student staging, pool plan, voxel index,
+# sort scratch) are looked for with 4 KB canaries on both sides of each workspace; check_guards() verifies them.
+_GUARD = os.environ.get("GEOPURIFY_B200_GUARD", "0") == "1"
+_GUARD_BYTES, _GUARD_BYTE = 4096, 0xA5
+_guarded = []
+
+
+def guard_workspaces(on=True):
+    global _GUARD
+    _GUARD = bool(on)
+    _guarded.clear()
+
+
 def _ws(nbytes):
-    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=_dev())
+    n = max(int(nbytes), 256)
+    if not _GUARD:
+        return torch.empty(n, dtype=torch.uint8, device=_dev())
+    n = (n + 255) // 256 * 256
+    raw = torch.empty(n + 2 * _GUARD_BYTES, dtype=torch.uint8, device=_dev())
+    raw[:_GUARD_BYTES] = _GUARD_BYTE
+    raw[_GUARD_BYTES + n:] = _GUARD_BYTE
+    _guarded.append((raw, n))
+    return raw[_GUARD_BYTES:_GUARD_BYTES + n]      # 4096-byte offset keeps the 256-byte alignment the C ABI asks for
+
+
+def check_guards():
+    """Verify the canaries of every workspace handed out since guard_workspaces(True) (synchronises).
+    Returns the number of workspaces checked; raises GeoPurifyError on the first damaged band."""
+    torch.cuda.synchronize()
+    for i, (raw, n) in enumerate(_guarded):
+        lo, hi = raw[:_GUARD_BYTES], raw[_GUARD_BYTES + n:]
+        if not bool((lo == _GUARD_BYTE).all()) or not bool((hi == _GUARD_BYTE).all()):
+            side = "below" if not bool((lo == _GUARD_BYTE).all()) else "above"
+            raise L.GeoPurifyError(f"workspace #{i} ({n} bytes): guard band {side} it was overwritten")
+    k = len(_guarded)
+    _guarded.clear()
+    return k
 
 
 def cameras_to_device(w2c, intr):

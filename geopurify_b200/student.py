@@ -168,7 +168,7 @@ class AffinityPredictor(nn.Module):
             nb = lib.gp_student_tc_workspace_bytes(ctypes.byref(desc), m)
             if nb == 0:
                 raise L.GeoPurifyError("student: layer structure not supported by the tensor-core path")
-            ws = torch.empty(nb, dtype=torch.uint8, device=x.device)
+            ws = ops._ws(nb)
             L.check(lib.gp_student_forward_tc(ctypes.byref(desc), L.ptr(flat), L.ptr(self._packed_tc), L.ptr(x),
                                               x.stride(0), L.ptr(nbr27), m, L.ptr(embed), int(normalize), L.ptr(ws),
                                               nb, L.stream()))
@@ -176,7 +176,7 @@ class AffinityPredictor(nn.Module):
             L.count(6 + 2 * nslab * (desc.n_layers - 1) + 2)
             return embed
         nb = lib.gp_student_workspace_bytes(ctypes.byref(desc), m)
-        ws = torch.empty(max(nb, 256), dtype=torch.uint8, device=x.device)
+        ws = ops._ws(nb)
         L.check(lib.gp_student_forward(ctypes.byref(desc), L.ptr(flat), L.ptr(x), x.stride(0), L.ptr(nbr27), m,
                                        L.ptr(embed), int(normalize), L.ptr(ws), nb, L.stream()))
         L.count(3 + 27 * 8 + 1 + 9 + 9 + 1)

@@ -14,7 +14,9 @@ WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
         "sm__inst_executed_pipe_tensor.sum", "lts__t_bytes.sum", "l1tex__t_sector_hit_rate.pct",
         "lts__t_sector_hit_rate.pct", "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
-        "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__cycles_active.avg"]
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__cycles_active.avg",
+        "lts__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
+        "l1tex__m_xbar2l1tex_read_bytes.sum", "l1tex__m_l1tex2xbar_write_bytes.sum", "sm__cycles_elapsed.avg.per_second"]
 
 
 def launches(path):

@@ -229,3 +229,17 @@ def test_fullsize_lifting_and_fill(full_run):
     assert 0.3 < float(seen.float().mean()) < 1.0
     assert bool((lifted.abs().sum(1) > 0).all()), "a point kept a zero feature after the fill"
     assert bool(torch.isfinite(lifted).all())
+
+
+def test_fullsize_workspace_guard_bands(full_run):
+    """Headline-size run (single 131072-voxel student slab, 1018 pooling tiles, 150k-point fill grid) with canaries
+    around every workspace -- the substitute for compute-sanitizer memcheck, which is closed on the build pool."""
+    from geopurify_b200 import ops
+    r = full_run
+    ops.guard_workspaces(True)
+    try:
+        again = r["model"].run_scene(r["s"], ignore=r["ign"])
+        assert ops.check_guards() >= 8
+        assert torch.equal(again["labels_voxel"], r["out"]["labels_voxel"])
+    finally:
+        ops.guard_workspaces(False)

@@ -868,3 +868,34 @@ def test_out_of_range_inputs_are_flagged_not_written_out_of_bounds(gp):
     tgt = torch.tensor([0, 1, 0], dtype=torch.int64, device="cuda")
     hist, _ = gp.iou_hist(lab, None, tgt, None, 2)
     assert hist.cpu().tolist() == [[1, 1], [2, 2], [2, 1]]
+
+
+def test_workspace_guard_bands_survive_whole_path(gp, small_scene, small_state):
+    """compute-sanitizer is closed on the build pool; instead every workspace (student staging / pair tables, pool plan
+    and planes, voxel index, sort scratch, fill grid, consensus scratch) gets 4 KB canaries on both sides, the whole
+    path runs, and the canaries must be intact: an internal index running past a workspace would land in them."""
+    from geopurify_b200.affinity_module import SonataXAffinityTrainer, scene_inputs_from_synth
+    from geopurify_b200.student import AffinityPredictor, load_numpy_state
+    sc = small_scene
+    gp.guard_workspaces(True)
+    try:
+        for lifting in ("mean", "consensus"):
+            model = SonataXAffinityTrainer(text_features=sc.text, logit_scale=sc.logit_scale, feature_dim=128, K=16,
+                                           n_pool=3, min_visible=50, lifting=lifting,
+                                           student=load_numpy_state(AffinityPredictor(134, 128, 128), small_state))
+            s = scene_inputs_from_synth(sc, feat_dtype=torch.float32)
+            ign = torch.tensor([sc.ignore_label], dtype=torch.int64, device="cuda")
+            model.run_scene(s, ignore=ign)
+        xyz = torch.as_tensor(sc.coords).cuda()
+        gp.knn_points(xyz[:4000].contiguous(), 16)
+        checked = gp.check_guards()
+        assert checked >= 12, checked
+        # the check itself works: damage a band on purpose
+        gp.guard_workspaces(True)
+        w = gp._ws(1000)
+        w.data_ptr()
+        gp._guarded[-1][0][5] = 0
+        with pytest.raises(Exception, match="guard band"):
+            gp.check_guards()
+    finally:
+        gp.guard_workspaces(False)
