@@ -228,63 +228,10 @@ extern "C" int gp_kernel_map(const void* index_workspace, int64_t m, int ex, int
 // One query per warp.  Keys are (d^2 << SHIFT) | original index: ascending key order is "ascending (d^2, index)".
 // KT = uint32 (SHIFT 21: index < 2^21, d^2 < 2^11) halves the shuffle traffic of the bitonic networks; it gives up
 // (returns false, the caller re-runs the query with 64-bit keys) when the search radius would need d^2 >= 2^11.
-// Pre-pass of a query: histogram of the squared distances (< 64) of the candidates in the two innermost cell shells
-// (shared memory, one 64-bin table per warp) -> the smallest d* with at least K candidates at d^2 <= d*.  Used only as
-// a FILTER for the search proper ("key < (d* + 1) << SHIFT"): every member of the true top K has a key below the K-th
-// smallest key among the scanned candidates, so nothing that belongs to the result is dropped, while the candidates
-// that reach the bitonic merges shrink from "everything until the list tightens" (~5 merges of 128 at K = 96) to K plus
-// the ties at d* (1-2 merges).  Returns 0xffffffff when the two shells hold fewer than K candidates below 64.
-__device__ __forceinline__ uint32_t knn_prefilter(const int4* __restrict__ sorted, const int2* __restrict__ cells,
-                                                  int64_t s, const int4 q, int cx, int cy, int cz, int K,
-                                                  uint32_t* hist, int lane) {
-  hist[lane] = 0;
-  hist[lane + 32] = 0;
-  __syncwarp();
-  const int qcx = q.x >> GP_CELL_SHIFT, qcy = q.y >> GP_CELL_SHIFT, qcz = q.z >> GP_CELL_SHIFT;
-  {
-    const int t = lane;   // the 27 cells of shells 0 and 1
-    int2 ce = make_int2(0, 0);
-    if (t < 27) {
-      int x = qcx + t % 3 - 1, y = qcy + (t / 3) % 3 - 1, z = qcz + t / 9 - 1;
-      if (x >= 0 && y >= 0 && z >= 0 && x < cx && y < cy && z < cz) ce = __ldg(&cells[((int64_t)z * cy + y) * cx + x]);
-    }
-    unsigned nonempty = __ballot_sync(0xffffffffu, ce.y > ce.x);
-    while (nonempty) {
-      int src = __ffs(nonempty) - 1;
-      nonempty &= nonempty - 1;
-      int beg = __shfl_sync(0xffffffffu, ce.x, src), end = __shfl_sync(0xffffffffu, ce.y, src);
-      for (int j = beg + lane; j < end; j += 32) {
-        if (j == s) continue;
-        int4 c = __ldg(&sorted[j]);
-        int dx = c.x - q.x, dy = c.y - q.y, dz = c.z - q.z;
-        unsigned d2 = (unsigned)(dx * dx) + (unsigned)(dy * dy) + (unsigned)(dz * dz);
-        if (d2 < 64u) atomicAdd(&hist[d2], 1u);
-      }
-    }
-  }
-  __syncwarp();
-  // inclusive prefix over the 64 bins (two per lane), then the first bin whose running count reaches K
-  const uint32_t a = hist[2 * lane], b = hist[2 * lane + 1];
-  uint32_t run = a + b;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t y = __shfl_up_sync(0xffffffffu, run, o);
-    if (lane >= o) run += y;
-  }
-  const uint32_t before = run - a - b;
-  int bin = 64;
-  if (before + a >= (uint32_t)K) bin = 2 * lane;
-  else if (run >= (uint32_t)K) bin = 2 * lane + 1;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) bin = min(bin, __shfl_xor_sync(0xffffffffu, bin, o));
-  __syncwarp();
-  return bin < 64 ? (uint32_t)(bin + 1) : 0xffffffffu;
-}
-
 template <typename KT, int SHIFT>
 __device__ __forceinline__ bool knn_query(const int4* __restrict__ sorted, const int2* __restrict__ cells, int64_t s,
                                           const int4 q, int cx, int cy, int cz, int K, KT* buf, int lane,
-                                          KT (&list)[4], KT filter = (KT)~(KT)0) {
+                                          KT (&list)[4]) {
   constexpr KT KMAX = (KT)~(KT)0;
   constexpr long long D2_LIMIT = sizeof(KT) == 4 ? (1ll << (32 - SHIFT)) - 1 : (1ll << 31);
   const int qcx = q.x >> GP_CELL_SHIFT, qcy = q.y >> GP_CELL_SHIFT, qcz = q.z >> GP_CELL_SHIFT;
@@ -296,8 +243,7 @@ __device__ __forceinline__ bool knn_query(const int4* __restrict__ sorted, const
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) list[j] = KMAX;
-  KT thr = KMAX;     // K-th smallest key merged so far (KMAX while fewer than K are in the list)
-  KT pass = filter;  // a candidate is buffered iff key < pass = min(filter, thr)
+  KT thr = KMAX;
   int nbuf = 0, merged = 0;
   const int rmax = max(cx, max(cy, cz));
   for (int r = 0; r <= rmax; ++r) {
@@ -328,7 +274,7 @@ __device__ __forceinline__ bool knn_query(const int4* __restrict__ sorted, const
             // candidates too far for the key width can only matter if the search runs past D2_LIMIT (-> false below)
             if ((long long)d2 <= D2_LIMIT - 1) key = ((KT)d2 << SHIFT) | (KT)(unsigned)c.w;
           }
-          bool take = key < pass;
+          bool take = key < thr;
           unsigned bal = __ballot_sync(0xffffffffu, take);
           if (take) buf[nbuf + __popc(bal & ((1u << lane) - 1))] = key;
           nbuf += __popc(bal);
@@ -338,7 +284,6 @@ __device__ __forceinline__ bool knn_query(const int4* __restrict__ sorted, const
             merged += nbuf;
             nbuf = 0;
             thr = topk_element(list, K - 1);
-            pass = thr < filter ? thr : filter;
             __syncwarp();
           }
         }
@@ -352,7 +297,6 @@ __device__ __forceinline__ bool knn_query(const int4* __restrict__ sorted, const
       merged += nbuf;
       nbuf = 0;
       thr = topk_element(list, K - 1);
-      pass = thr < filter ? thr : filter;
       __syncwarp();
     }
     long long g = (long long)r * GP_CELL + 1 + slack;
@@ -370,7 +314,6 @@ __global__ void __launch_bounds__(KNN_WARPS * 32) knn_grid_kernel(const int4* __
                                                                    int32_t* __restrict__ nbr_orig,
                                                                    int32_t* __restrict__ nbr_sorted) {
   __shared__ u64 sbuf[KNN_WARPS][128];
-  __shared__ uint32_t shist[KNN_WARPS][64];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t s = (int64_t)blockIdx.x * KNN_WARPS + warp;
   if (s >= m) return;
@@ -379,9 +322,7 @@ __global__ void __launch_bounds__(KNN_WARPS * 32) knn_grid_kernel(const int4* __
   bool done = false;
   if (m <= (1ll << 21)) {  // 32-bit keys: 21 index bits, 11 distance bits
     uint32_t list[4];
-    const uint32_t dstar = knn_prefilter(sorted, cells, s, q, cx, cy, cz, K, shist[warp], lane);
-    const uint32_t filter = dstar == 0xffffffffu ? 0xffffffffu : (dstar << 21);
-    done = knn_query<uint32_t, 21>(sorted, cells, s, q, cx, cy, cz, K, (uint32_t*)sbuf[warp], lane, list, filter);
+    done = knn_query<uint32_t, 21>(sorted, cells, s, q, cx, cy, cz, K, (uint32_t*)sbuf[warp], lane, list);
 #pragma unroll
     for (int j = 0; j < 4; ++j) orig[j] = (int)(list[j] & 0x1fffffu);
   }

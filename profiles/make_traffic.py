@@ -10,10 +10,9 @@ import subprocess
 import sys
 
 out = {}
-note = ""
+note = " ".join(a for a in sys.argv[1:] if "=" not in a)
 for arg in sys.argv[1:]:
     if "=" not in arg:
-        note = arg
         continue
     name, path = arg.split("=", 1)
     txt = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
