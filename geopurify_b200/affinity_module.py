@@ -251,6 +251,30 @@ class SonataXAffinityTrainer:
 GeoPurifyB200 = SonataXAffinityTrainer
 
 
+class InterleavedScenes:
+    """Runs a stream of independent device-resident scenes on `n_streams` CUDA streams, scene i on stream i mod n, so
+    that the short latency-bound stages of one scene (index build, sorts, fill, projection) can run beside the
+    persistent tensor-core kernels of another.  Results are identical to calling `run_scene` per scene: each scene's
+    tensors live on its own stream (the caching allocator is stream-aware) and the shared histogram block is only
+    touched by int64 atomics."""
+
+    def __init__(self, model, n_streams=2):
+        self.model = model
+        self.streams = [torch.cuda.Stream() for _ in range(max(1, int(n_streams)))]
+
+    def run(self, scenes, hist=None, ignore=None):
+        main = torch.cuda.current_stream()
+        for st in self.streams:
+            st.wait_stream(main)
+        outs = []
+        for i, s in enumerate(scenes):
+            with torch.cuda.stream(self.streams[i % len(self.streams)]):
+                outs.append(self.model.run_scene(s, hist=hist, ignore=ignore))
+        for st in self.streams:
+            main.wait_stream(st)
+        return outs
+
+
 def scene_inputs_from_synth(scene, feat_dtype=torch.bfloat16, device="cuda", coords_f64=True):
     """Upload a `geopurify_b200.synth.Scene` (host numpy) to the device in the layout `run_scene` expects.
     The dense feature map is the table lookup of the id map -- the stand-in for the 2-D VLM output."""

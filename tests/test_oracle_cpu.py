@@ -97,6 +97,30 @@ def test_kernel_map_variants_agree():
     assert (nb[:, 13] == np.arange(len(c))).all()
 
 
+def test_sparse_conv_offset_convention_delta_response():
+    """Pins the one convention of the stubbed MinkowskiEngine operator that could silently permute a released
+    checkpoint: `MinkowskiConvolution.kernel` is [kernel_volume, Cin, Cout] and kernel index
+    o enumerates the 3^3 region with the FIRST spatial axis fastest, o = (dx+1) + 3 (dy+1) + 9 (dz+1) (ME docs,
+    "MinkowskiConvolution" / "KernelGenerator": region offsets in lexicographic order of reversed axes; this is the
+    documented layout, not verified against ME itself -- ME is not installable here).  A centred one-hot input then
+    answers, at the voxel displaced by -delta_o, with row 0 of W_o: out[i] = sum_o W_o^T x[i + delta_o]."""
+    g = np.stack(np.meshgrid(np.arange(3), np.arange(3), np.arange(3), indexing="ij"), -1).reshape(-1, 3)
+    rng = np.random.default_rng(0)
+    g = g[rng.permutation(27)]                                   # row order must not matter
+    centre = int(np.nonzero((g == 1).all(1))[0][0])
+    for nbr in (oracle.kernel_map(g), oracle.kernel_map_fast(g)):
+        x = torch.zeros(27, 2)
+        x[centre, 0] = 1.0
+        w = torch.zeros(27, 2, 3)
+        w[:, 0, :] = torch.arange(1, 28, dtype=torch.float32)[:, None] * torch.tensor([1.0, 10.0, 100.0])
+        out = oracle.sparse_conv3(x, w, nbr)
+        for o in range(27):
+            d = np.array([o % 3 - 1, (o // 3) % 3 - 1, o // 9 - 1])          # x fastest
+            i = int(np.nonzero((g == 1 - d).all(1))[0][0])                   # the voxel that sees the centre at +delta_o
+            assert torch.equal(out[i], w[o, 0]), (o, d, out[i], w[o, 0])
+        assert nbr[centre, 13] == centre and (nbr[centre] >= 0).all()
+
+
 def test_pool_rows_are_convex_combinations():
     rng = np.random.default_rng(3)
     m, k = 300, 8
