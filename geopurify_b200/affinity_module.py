@@ -372,8 +372,11 @@ class HostScenePipeline:
     still pays its full host->device and device->host traffic -- the copies overlap the previous / next scene's
     kernels instead of serialising with them.  Results are identical to calling `run_scene_host` per scene."""
 
-    def __init__(self, model, ignore, feat_dtype=torch.bfloat16, dense=None):
+    def __init__(self, model, ignore, feat_dtype=torch.bfloat16, dense=None, n_streams=2):
         self.model, self.ignore, self.feat_dtype = model, ignore, feat_dtype
+        # scenes alternate between `n_streams` compute streams (as InterleavedScenes): the short stages of one scene run
+        # beside the tensor-core kernels of the other
+        self.compute = [torch.cuda.Stream() for _ in range(max(1, int(n_streams)))]
         # the compact (id map, table) form is lifted directly; dense=True expands it to [V,H,W,D] maps first
         self.dense = False if dense is None else dense
         self.copy_in = torch.cuda.Stream()
@@ -390,9 +393,9 @@ class HostScenePipeline:
         return buf[:n].view(shape)
 
     def _upload(self, h, slot):
-        main = torch.cuda.current_stream()
         with torch.cuda.stream(self.copy_in):
-            self.copy_in.wait_stream(main)            # buffers of slot are free once earlier main-stream work is done
+            for st in self.compute:                   # buffers of slot are free once earlier compute work is done
+                self.copy_in.wait_stream(st)
             fo = self._feat[slot]
             if self.dense and fo is not None:
                 V, (W, H) = h.t["idmaps"].shape[0], h.image_dim
@@ -410,21 +413,25 @@ class HostScenePipeline:
     def run(self, hosts):
         """hosts: sequence of HostScene.  Returns [(pred [N] int64 pinned CPU, hist [3,C] int64 pinned CPU), ...]."""
         hosts = list(hosts)
-        out, pending = [], []
-        main = torch.cuda.current_stream()
+        out = []
+        caller = torch.cuda.current_stream()
+        for st in self.compute:
+            st.wait_stream(caller)
         nxt = self._upload(hosts[0], 0) if hosts else None
         for i, h in enumerate(hosts):
             s, ev = nxt
-            main.wait_event(ev)
+            comp = self.compute[i % len(self.compute)]
+            comp.wait_event(ev)
             for t in (s.coords, s.feat, s.depth, s.idmaps, s.tables, s.labels, s.voxel_coords, s.p2v, s.gauss,
                       s.coords_f32, s.w2c, s.intr):
                 if t is not None:
-                    t.record_stream(main)
+                    t.record_stream(comp)
             if i + 1 < len(hosts):
                 nxt = self._upload(hosts[i + 1], (i + 1) & 1)
-            res = self.model.run_scene(s, ignore=self.ignore, want_pred=True)
-            done = torch.cuda.Event()
-            done.record(main)
+            with torch.cuda.stream(comp):
+                res = self.model.run_scene(s, ignore=self.ignore, want_pred=True)
+                done = torch.cuda.Event()
+                done.record(comp)
             with torch.cuda.stream(self.copy_out):
                 self.copy_out.wait_event(done)
                 # one pinned staging buffer per scene of the batch, reused by later run() calls
@@ -436,4 +443,6 @@ class HostScenePipeline:
                 res["hist"].record_stream(self.copy_out)
             out.append((pred, hist))
         self.copy_out.synchronize()
+        for st in self.compute:
+            caller.wait_stream(st)
         return out

@@ -899,3 +899,25 @@ def test_workspace_guard_bands_survive_whole_path(gp, small_scene, small_state):
             gp.check_guards()
     finally:
         gp.guard_workspaces(False)
+
+
+def test_interleaved_scenes_equal_sequential(gp, small_scene, small_state):
+    """affinity_module.InterleavedScenes (the bench's two-stream form) returns exactly what run_scene returns scene by
+    scene: labels, pooled features, and the shared histogram block."""
+    from geopurify_b200.affinity_module import InterleavedScenes, SonataXAffinityTrainer, scene_inputs_from_synth
+    from geopurify_b200.student import AffinityPredictor, load_numpy_state
+    scenes = [small_scene, synth.make_scene(n_points=9000, n_views=5, image_dim=(80, 60), seed=4, room=(2.0, 1.6, 2.0),
+                                            n_boxes=2, cut=2, q_range=(4, 12), feat_dim=128, n_classes=7)]
+    model = SonataXAffinityTrainer(text_features=small_scene.text, logit_scale=small_scene.logit_scale, feature_dim=128,
+                                   K=16, n_pool=3, min_visible=50,
+                                   student=load_numpy_state(AffinityPredictor(134, 128, 128), small_state))
+    ins = [scene_inputs_from_synth(sc, feat_dtype=torch.float32) for sc in scenes] * 3
+    ign = torch.tensor([small_scene.ignore_label], dtype=torch.int64, device="cuda")
+    h_seq = torch.zeros((3, 7), dtype=torch.int64, device="cuda")
+    seq = [model.run_scene(s, hist=h_seq, ignore=ign) for s in ins]
+    h_int = torch.zeros((3, 7), dtype=torch.int64, device="cuda")
+    inter = InterleavedScenes(model, 2).run(ins, hist=h_int, ignore=ign)
+    torch.cuda.synchronize()
+    assert torch.equal(h_seq, h_int)
+    for a, b in zip(seq, inter):
+        assert torch.equal(a["labels_voxel"], b["labels_voxel"]) and torch.equal(a["pooled"], b["pooled"])
