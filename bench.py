@@ -330,16 +330,21 @@ def fixed_list_arm(args, torch, dist, rank, world, local, model, hosts, resident
         return tot, [round(float(b[1]), 2) for b in busy]
 
     l0 = _lib.launch_count
+    allocs0 = torch.cuda.memory_stats().get("num_device_alloc", 0)
     sampler.mark_begin()
     if args.streams > 1:
         from geopurify_b200.affinity_module import InterleavedScenes
         inter = InterleavedScenes(model, args.streams)
         inter.run([resident[i] for i in range(len(hosts))], hist=hist, ignore=ign)     # warm the side streams
-        ms, busy = timed(lambda: inter.run([resident[a] for a in seq], hist=hist, ignore=ign))
+        ms, busy = timed(lambda: inter.run([resident[a] for a in seq], hist=hist, ignore=ign, collect=False))
     else:
-        ms, busy = timed(lambda: [model.run_scene(resident[a], hist=hist, ignore=ign) for a in seq])
+        def body_seq():
+            for a in seq:
+                model.run_scene(resident[a], hist=hist, ignore=ign)
+        ms, busy = timed(body_seq)
     sampler.mark_end()
     launches = _lib.launch_count - l0
+    cuda_mallocs = torch.cuda.memory_stats().get("num_device_alloc", 0) - allocs0
     clocks = sampler.stop() if rank == 0 else None
     hsum = hist.cpu().numpy()
     miou = mean_iou(hsum[0], hsum[1], hsum[2])
@@ -375,7 +380,8 @@ def fixed_list_arm(args, torch, dist, rank, world, local, model, hosts, resident
                     "scenes_per_s": args.scenes / (ms_e2e * 1e-3), "rank_busy_ms": busy_e2e,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "geopurify_b200.affinity_module.HostScenePipeline.run + validation.reduce_histograms"},
-            "gpu_launches": launches, "clocks": clocks, "miou_synthetic": miou[0],
+            "gpu_launches": launches, "cuda_mallocs_in_timed_region": cuda_mallocs, "clocks": clocks,
+            "miou_synthetic": miou[0],
         }
         print(json.dumps(line))
     if world > 1:
@@ -471,7 +477,7 @@ def ours_arm(args):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        inter.run([resident[i % len(hosts)] for i in range(args.steps)], hist=hist, ignore=ign)
+        inter.run([resident[i % len(hosts)] for i in range(args.steps)], hist=hist, ignore=ign, collect=False)
         if world > 1:
             dist.all_reduce(hist)
         e1.record()

@@ -164,13 +164,17 @@ class SonataXAffinityTrainer:
     def purify(self, lifted, gauss, voxel_coords_i32, p2v_i32, extent, keep_intermediates=False):
         """Voxel scatter-mean, student, kNN, affinity softmax, pooling (models/affinity_module.py:1524-1589).
         Returns (pooled [M,D] in sorted voxel order, p2v_sorted [N] int32)."""
+        with ops.scratch(not keep_intermediates):
+            return self._purify(lifted, gauss, voxel_coords_i32, p2v_i32, extent, keep_intermediates)
+
+    def _purify(self, lifted, gauss, voxel_coords_i32, p2v_i32, extent, keep_intermediates):
         d = self.feature_dim
         m = voxel_coords_i32.shape[0]
         index = ops.VoxelIndex(voxel_coords_i32, extent)
         p2v_sorted = index.rank[p2v_i32.long()].contiguous()
         plan = ops.ScatterPlan(p2v_sorted, m)
         stride = self.affinity_student.input_stride
-        vin = torch.empty((m, stride), dtype=torch.float32, device=lifted.device)
+        vin = ops._new((m, stride), torch.float32, "vin")
         if stride > d + 6:
             vin[:, d + 6:].zero_()       # only the pad columns: the two scatter-means write every other element
         plan.mean(lifted, d, vin, 0)
@@ -216,6 +220,10 @@ class SonataXAffinityTrainer:
     def run_scene(self, s: SceneInputs, hist=None, ignore=None, keep_intermediates=False, want_pred=False):
         """Stages 1a-4 on the device: fused project + gather-mean, fill, purify, per-voxel classification,
         label gather + IoU histograms.  Returns dict(labels_voxel, p2v_sorted, hist, seen)."""
+        with ops.scratch(not keep_intermediates):
+            return self._run_scene(s, hist, ignore, keep_intermediates, want_pred)
+
+    def _run_scene(self, s, hist, ignore, keep_intermediates, want_pred):
         W, H = s.image_dim
         d = self.feature_dim
         self._mark("begin")
@@ -262,14 +270,19 @@ class InterleavedScenes:
         self.model = model
         self.streams = [torch.cuda.Stream() for _ in range(max(1, int(n_streams)))]
 
-    def run(self, scenes, hist=None, ignore=None):
+    def run(self, scenes, hist=None, ignore=None, collect=True):
+        """`collect=False` drops every scene's result dict at once (an evaluation that only wants the accumulated
+        `hist` would otherwise keep one [M,512] pooled tensor per scene alive)."""
         main = torch.cuda.current_stream()
         for st in self.streams:
             st.wait_stream(main)
         outs = []
         for i, s in enumerate(scenes):
             with torch.cuda.stream(self.streams[i % len(self.streams)]):
-                outs.append(self.model.run_scene(s, hist=hist, ignore=ignore))
+                r = self.model.run_scene(s, hist=hist, ignore=ignore)
+                if collect:
+                    outs.append(r)
+                del r
         for st in self.streams:
             main.wait_stream(st)
         return outs

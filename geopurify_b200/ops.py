@@ -25,16 +25,71 @@ _GUARD_BYTES, _GUARD_BYTE = 4096, 0xA5
 _guarded = []
 
 
+# Scene-internal temporaries (pixel table, lifted rows, voxel rows, kernel map, embeddings, neighbour lists, weights,
+# index tables) can come from the same grow-only arena while `scratch()` is active: run_scene / purify switch it on when
+# the caller did not ask to keep intermediates, so an evaluation list of differently sized scenes issues no cudaMalloc
+# after its largest scene (the caching allocator splits and re-grows its blocks otherwise: ~1.3 cudaMalloc per scene on
+# the 312-scene list).  Tensors handed back to the caller (pooled features, labels, seen flags, predictions, histograms)
+# are always fresh allocations.
+_SCRATCH = False
+_ITEM = {torch.uint8: 1, torch.int32: 4, torch.float32: 4, torch.int64: 8, torch.float64: 8, torch.bfloat16: 2}
+
+
+class scratch:
+    def __init__(self, on=True):
+        self.on = bool(on)
+
+    def __enter__(self):
+        global _SCRATCH
+        self.prev = _SCRATCH
+        _SCRATCH = self.on or self.prev
+        return self
+
+    def __exit__(self, *exc):
+        global _SCRATCH
+        _SCRATCH = self.prev
+        return False
+
+
+def _new(shape, dtype, tag):
+    """Output tensor of a wrapper: a fresh allocation, or (inside `scratch()`) a view of the arena buffer `tag`."""
+    if not _SCRATCH or _GUARD:
+        return torch.empty(shape, dtype=dtype, device=_dev())
+    n = 1
+    for d in shape:
+        n *= int(d)
+    item = _ITEM[dtype]
+    return _ws(max(n * item, 256), "out:" + tag)[: n * item].view(dtype).view(shape)
+
+
 def guard_workspaces(on=True):
     global _GUARD
     _GUARD = bool(on)
     _guarded.clear()
 
 
-def _ws(nbytes):
+# Call-scoped workspaces come from a grow-only arena, one buffer per (device, stream, call site): scenes of different
+# sizes would otherwise ask the caching allocator for a different multi-GB block each (the student's worst-case pair
+# staging alone is 54 KB per voxel), which ends in cudaMalloc / cudaFree stalls in the middle of an evaluation list.
+# Reuse is safe because a workspace is only touched by kernels the call enqueues on its stream, and the next call with
+# the same tag on that stream is ordered behind them.  Workspaces that outlive the call (VoxelIndex, ScatterPlan) are
+# plain allocations.
+_arena = {}
+
+
+def _ws(nbytes, tag=None):
     n = max(int(nbytes), 256)
     if not _GUARD:
-        return torch.empty(n, dtype=torch.uint8, device=_dev())
+        if tag is None:
+            return torch.empty(n, dtype=torch.uint8, device=_dev())
+        key = (torch.cuda.current_device(), torch.cuda.current_stream().cuda_stream, tag)
+        buf = _arena.get(key)
+        if buf is None or buf.numel() < n:
+            _arena.pop(key, None)
+            buf = None
+            buf = torch.empty(int(n * 1.25) + 4096, dtype=torch.uint8, device=_dev())
+            _arena[key] = buf
+        return buf[:n]
     n = (n + 255) // 256 * 256
     raw = torch.empty(n + 2 * _GUARD_BYTES, dtype=torch.uint8, device=_dev())
     raw[:_GUARD_BYTES] = _GUARD_BYTE
@@ -70,8 +125,8 @@ def project_views(coords, w2c, intr, depth, H, W, cut, vis_thres):
     """A1: returns pix [V,N] int32 (row*W+col or -1) and counts [V] int32."""
     lib = L.load()
     n, V = coords.shape[0], w2c.shape[0]
-    pix = torch.empty((V, n), dtype=torch.int32, device=_dev())
-    counts = torch.empty((V,), dtype=torch.int32, device=_dev())
+    pix = _new((V, n), torch.int32, "pix")
+    counts = _new((V,), torch.int32, "counts")
     dd = 0 if depth is None else L.dtype_code(depth)
     L.check(lib.gp_project_views(L.ptr(coords), L.dtype_code(coords), n, L.ptr(w2c), L.ptr(intr), L.ptr(depth), dd, V,
                                  H, W, cut, float(vis_thres), L.ptr(pix), L.ptr(counts), L.stream()))
@@ -99,7 +154,7 @@ def splat_depth(coords, w2c, intr, H, W, cut):
 
 def accept_views(counts, min_visible=400, max_visible=2**31 - 1):
     lib = L.load()
-    keep = torch.empty((counts.shape[0],), dtype=torch.uint8, device=_dev())
+    keep = _new((counts.shape[0],), torch.uint8, "keep")
     L.check(lib.gp_accept_views(L.ptr(counts), counts.shape[0], int(min_visible), int(max_visible), L.ptr(keep),
                                 L.stream()))
     L.count(1)
@@ -136,7 +191,7 @@ def visible_csr(pix, keep, W, want_pixels=True):
     rows = torch.empty((cap,), dtype=torch.int32, device=_dev()) if want_pixels else None
     cols = torch.empty((cap,), dtype=torch.int32, device=_dev()) if want_pixels else None
     nb = lib.gp_visible_csr_workspace_bytes(n, V)
-    ws = _ws(nb)
+    ws = _ws(nb, "visible_csr")
     L.check(lib.gp_visible_csr(L.ptr(pix), L.ptr(keep), n, V, W, L.ptr(off), L.ptr(pidx), L.ptr(vidx), L.ptr(rows),
                                L.ptr(cols), L.ptr(ws), nb, L.stream()))
     L.count(4)
@@ -150,7 +205,7 @@ def lift_mean_fused(coords, w2c, intr, depth, H, W, cut, vis_thres, keep, feat, 
     n, V, D = coords.shape[0], w2c.shape[0], feat.shape[-1]
     if out is None:
         out_stride = out_stride or D
-        out = torch.empty((n, out_stride), dtype=torch.float32, device=_dev())
+        out = _new((n, out_stride), torch.float32, "lifted")
     seen = torch.empty((n,), dtype=torch.uint8, device=_dev())
     dd = 0 if depth is None else L.dtype_code(depth)
     L.check(lib.gp_lift_mean_fused(L.ptr(coords), L.dtype_code(coords), n, L.ptr(w2c), L.ptr(intr), L.ptr(depth), dd,
@@ -168,7 +223,7 @@ def lift_mean_idmap(coords, w2c, intr, depth, H, W, cut, vis_thres, keep, idmap_
     Q, D = table.shape[1], table.shape[2]
     if out is None:
         out_stride = out_stride or D
-        out = torch.empty((n, out_stride), dtype=torch.float32, device=_dev())
+        out = _new((n, out_stride), torch.float32, "lifted")
     seen = torch.empty((n,), dtype=torch.uint8, device=_dev())
     dd = 0 if depth is None else L.dtype_code(depth)
     L.check(lib.gp_lift_mean_idmap(L.ptr(coords), L.dtype_code(coords), n, L.ptr(w2c), L.ptr(intr), L.ptr(depth), dd,
@@ -197,7 +252,7 @@ def lift_mean_pix(pix, keep, feat, H, W, out=None, out_stride=None):
     D = feat.shape[-1]
     if out is None:
         out_stride = out_stride or D
-        out = torch.empty((n, out_stride), dtype=torch.float32, device=_dev())
+        out = _new((n, out_stride), torch.float32, "lifted")
     seen = torch.empty((n,), dtype=torch.uint8, device=_dev())
     L.check(lib.gp_lift_mean_pix(L.ptr(pix), n, V, H, W, L.ptr(keep), L.ptr(feat), L.dtype_code(feat), D, L.ptr(out),
                                  out.stride(0), L.ptr(seen), L.stream()))
@@ -215,10 +270,10 @@ def lift_consensus(pix, keep, idmap_u8, table_f32, text, logit_scale, xyz_f32, c
     C = text.shape[0]
     if out is None:
         out_stride = out_stride or D
-        out = torch.empty((n, out_stride), dtype=torch.float32, device=_dev())
+        out = _new((n, out_stride), torch.float32, "lifted")
     seen = torch.empty((n,), dtype=torch.uint8, device=_dev())
     nb = lib.gp_lift_consensus_workspace_bytes(n, V, Q, D, C)
-    ws = _ws(nb)
+    ws = _ws(nb, "lift_consensus")
     L.check(lib.gp_lift_consensus(L.ptr(pix), n, V, H, W, L.ptr(keep), L.ptr(idmap_u8), L.ptr(table_f32), Q, D,
                                   L.ptr(text), C, float(logit_scale), L.ptr(xyz_f32), float(cell), L.ptr(out),
                                   out.stride(0), L.ptr(seen), L.ptr(ws), nb, L.stream()))
@@ -230,9 +285,9 @@ def nn1_fill(xyz, seen, cell=0.05):
     """Nearest seen point of every unseen point: nn [N] int32 (nn[i]=i when seen)."""
     lib = L.load()
     n = xyz.shape[0]
-    nn = torch.empty((n,), dtype=torch.int32, device=_dev())
+    nn = _new((n,), torch.int32, "nn1")
     nb = lib.gp_nn1_fill_workspace_bytes(n)
-    ws = _ws(nb)
+    ws = _ws(nb, "nn1_fill")
     L.check(lib.gp_nn1_fill(L.ptr(xyz), n, L.ptr(seen), float(cell), L.ptr(nn), L.ptr(ws), nb, L.stream()))
     L.count(8)
     return nn
@@ -256,7 +311,7 @@ def voxelize(coords, xform):
     rec = torch.empty((n,), dtype=torch.int32, device=_dev())
     meta = torch.zeros((4,), dtype=torch.int64, device=_dev())   # m | extent as int32[3] in the next 12 bytes
     nb = lib.gp_voxelize_workspace_bytes(n)
-    ws = _ws(nb)
+    ws = _ws(nb, "voxelize")
     ext_ptr = ctypes.c_void_p(meta.data_ptr() + 8)
     L.check(lib.gp_voxelize(L.ptr(coords), L.dtype_code(coords), n, L.ptr(xf), L.ptr(vox), L.ptr(inds), L.ptr(rec),
                             L.ptr(meta), ext_ptr, L.ptr(ws), nb, L.stream()))
@@ -280,9 +335,9 @@ class VoxelIndex:
         if nb == 0:
             raise L.GeoPurifyError(f"voxel index: unsupported sizes m={self.m} extent={extent}")
         self.nbytes = nb
-        self.ws = _ws(nb)
-        self.order = torch.empty((self.m,), dtype=torch.int32, device=_dev())
-        self.rank = torch.empty((self.m,), dtype=torch.int32, device=_dev())
+        self.ws = _new((max(int(nb), 256),), torch.uint8, "index_ws") if not _GUARD else _ws(nb)
+        self.order = _new((self.m,), torch.int32, "index_order")
+        self.rank = _new((self.m,), torch.int32, "index_rank")
         L.check(lib.gp_voxel_index_build(L.ptr(vox_i32, torch.int32), self.m, self.ex, self.ey, self.ez,
                                          L.ptr(self.order), L.ptr(self.rank), L.ptr(self.ws), nb, L.stream()))
         L.count(8)
@@ -295,15 +350,15 @@ class VoxelIndex:
 
     def kernel_map(self):
         lib = L.load()
-        out = torch.empty((self.m, 27), dtype=torch.int32, device=_dev())
+        out = _new((self.m, 27), torch.int32, "nbr27")
         L.check(lib.gp_kernel_map(L.ptr(self.ws), self.m, self.ex, self.ey, self.ez, L.ptr(out), L.stream()))
         L.count(1)
         return out
 
     def knn(self, k, want_orig=True, want_sorted=True):
         lib = L.load()
-        no = torch.empty((self.m, k), dtype=torch.int32, device=_dev()) if want_orig else None
-        ns = torch.empty((self.m, k), dtype=torch.int32, device=_dev()) if want_sorted else None
+        no = _new((self.m, k), torch.int32, "knn_orig") if want_orig else None
+        ns = _new((self.m, k), torch.int32, "knn_sorted") if want_sorted else None
         L.check(lib.gp_knn_grid(L.ptr(self.ws), self.m, self.ex, self.ey, self.ez, k, L.ptr(no), L.ptr(ns), L.stream()))
         L.count(1)
         return no, ns
@@ -316,7 +371,7 @@ def knn_points(xyz_f32, k, min_cell=1e-3):
     n = xyz_f32.shape[0]
     out = torch.empty((n, k), dtype=torch.int32, device=_dev())
     nb = lib.gp_knn_points_workspace_bytes(n)
-    ws = _ws(nb)
+    ws = _ws(nb, "knn_points")
     L.check(lib.gp_knn_points(L.ptr(xyz_f32), n, k, float(min_cell), L.ptr(out), L.ptr(ws), nb, L.stream()))
     L.count(9)
     return out
@@ -333,7 +388,7 @@ def mine_contrastive(feat, anchors_i32, nbr_i32, n_macro=48, n_micro=15):
     nb = lib.gp_mine_workspace_bytes(n, d, a, n_macro)
     if nb == 0:
         raise L.GeoPurifyError(f"gp_mine_workspace_bytes: bad sizes n={n} D={d} A={a}")
-    ws = _ws(nb)
+    ws = _ws(nb, "mine")
     L.check(lib.gp_mine_contrastive(L.ptr(feat), feat.stride(0), d, n, L.ptr(anchors_i32), a, L.ptr(nbr_i32), k,
                                     n_macro, n_micro, L.ptr(pos), L.ptr(neg), L.ptr(ws), nb, L.stream()))
     L.count(6)
@@ -347,7 +402,7 @@ class ScatterPlan:
         lib = L.load()
         self.n, self.m = p2v_i32.shape[0], int(m)
         nb = lib.gp_scatter_mean_workspace_bytes(self.n, self.m)
-        self.ws = _ws(nb)
+        self.ws = _new((max(int(nb), 256),), torch.uint8, "scatter_ws") if not _GUARD else _ws(nb)
         L.check(lib.gp_scatter_mean_prepare(L.ptr(p2v_i32, torch.int32), self.n, self.m, L.ptr(self.ws), nb, L.stream()))
         L.count(6)
 
@@ -362,7 +417,7 @@ class ScatterPlan:
 def affinity_softmax(embed, nbr_sorted, sharpen=20.0):
     lib = L.load()
     m, k = nbr_sorted.shape
-    w = torch.empty((m, k), dtype=torch.float32, device=_dev())
+    w = _new((m, k), torch.float32, "weights")
     L.check(lib.gp_affinity_softmax(L.ptr(embed, torch.float32), embed.shape[1], L.ptr(nbr_sorted, torch.int32), m, k,
                                     float(sharpen), L.ptr(w),
                                     L.stream()))
@@ -384,11 +439,11 @@ def pool(f0, D, nbr_sorted, weights, T, tensor_core=None):
         tensor_core = D in (256, 512) and T >= 2
     if tensor_core:
         nbp = lib.gp_pool_plan_bytes(m, k)
-        plan = _ws(nbp)
+        plan = _ws(nbp, "pool_plan")
         L.check(lib.gp_pool_plan(L.ptr(nbr_sorted, torch.int32), L.ptr(weights, torch.float32), m, k, L.ptr(plan), nbp,
                                  L.stream()))
         nbw = lib.gp_pool_tc_workspace_bytes(m)
-        ws = _ws(nbw)
+        ws = _ws(nbw, "pool_ws")
         out = torch.empty((m, D), dtype=torch.float32, device=_dev())
         L.check(lib.gp_pool_tc(L.ptr(f0), f0.stride(0), D, L.ptr(plan), L.ptr(nbr_sorted), L.ptr(weights), m, k, T,
                                L.ptr(out), L.ptr(ws), nbw, L.stream()))
@@ -425,14 +480,14 @@ def logits_argmax(feat, D, text, logit_scale, want_logits=False, want_zero=True,
         tensor_core = (not want_logits) and C <= 256 and D % 128 == 0 and float(logit_scale) > 0 and rows > 0
     if tensor_core:
         nb = lib.gp_logits_tc_workspace_bytes(rows, C, D)
-        ws = _ws(nb)
+        ws = _ws(nb, "logits_tc")
         L.check(lib.gp_logits_argmax_tc(L.ptr(feat), feat.stride(0), D, rows, L.ptr(text), C, float(logit_scale),
                                         L.ptr(label), L.ptr(zero), L.ptr(ws), nb, L.stream()))
         L.count(6)
         return label, zero, None
     logits = torch.empty((rows, C), dtype=torch.float32, device=_dev()) if want_logits else None
     nb = lib.gp_logits_workspace_bytes(C, D)
-    ws = _ws(nb)
+    ws = _ws(nb, "logits")
     L.check(lib.gp_logits_argmax(L.ptr(feat), feat.stride(0), D, rows, L.ptr(text), C, float(logit_scale), L.ptr(label),
                                  L.ptr(zero), L.ptr(logits), L.ptr(ws), nb, L.stream()))
     L.count(2)

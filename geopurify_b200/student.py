@@ -158,7 +158,7 @@ class AffinityPredictor(nn.Module):
         m = x.shape[0]
         if x.stride(0) < self.input_stride:
             raise L.GeoPurifyError(f"student input rows need stride >= {self.input_stride} (zero padded)")
-        embed = torch.empty((m, self.embed_dim), dtype=torch.float32, device=x.device)
+        embed = ops._new((m, self.embed_dim), torch.float32, "embed")
         if self.precision == "bf16x3":
             if self._packed_tc is None or self._packed_tc.device != x.device:
                 nbp = lib.gp_student_tc_pack_bytes(ctypes.byref(desc))
@@ -168,7 +168,7 @@ class AffinityPredictor(nn.Module):
             nb = lib.gp_student_tc_workspace_bytes(ctypes.byref(desc), m)
             if nb == 0:
                 raise L.GeoPurifyError("student: layer structure not supported by the tensor-core path")
-            ws = ops._ws(nb)
+            ws = ops._ws(nb, "student_tc")
             L.check(lib.gp_student_forward_tc(ctypes.byref(desc), L.ptr(flat), L.ptr(self._packed_tc), L.ptr(x),
                                               x.stride(0), L.ptr(nbr27), m, L.ptr(embed), int(normalize), L.ptr(ws),
                                               nb, L.stream()))
@@ -176,7 +176,7 @@ class AffinityPredictor(nn.Module):
             L.count(6 + 2 * nslab * (desc.n_layers - 1) + 2)
             return embed
         nb = lib.gp_student_workspace_bytes(ctypes.byref(desc), m)
-        ws = ops._ws(nb)
+        ws = ops._ws(nb, "student")
         L.check(lib.gp_student_forward(ctypes.byref(desc), L.ptr(flat), L.ptr(x), x.stride(0), L.ptr(nbr27), m,
                                        L.ptr(embed), int(normalize), L.ptr(ws), nb, L.stream()))
         L.count(3 + 27 * 8 + 1 + 9 + 9 + 1)
