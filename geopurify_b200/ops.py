@@ -1,6 +1,8 @@
 """Thin torch-tensor wrappers over the C ABI: allocate outputs / workspaces, pass pointers, raise on error.
 
-Every function enqueues on the current CUDA stream and returns device tensors.
+Every function enqueues on the current CUDA stream and returns device tensors.  Like the reference (one Python
+thread per process, `torch.no_grad()`), the wrappers are not thread-safe: workspaces come from a per-stream grow-only
+arena (see `_ws` / `scratch`), so use one host thread per CUDA stream.
 """
 from __future__ import annotations
 

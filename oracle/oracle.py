@@ -23,7 +23,13 @@ Pinning status
     over occupied 3^3 offsets of W_d^T x, offsets x fastest, no bias; IndexFlatL2 = exact L2,
     ties by lowest index as the north star states.  The arithmetic INSIDE those three
     operators therefore rests on their documentation; everything around them is the
-    reference's code.  sklearn `KDTree` is the real library.
+    reference's code.  sklearn `KDTree` is the real library.  The offset convention of the
+    stubbed convolution is pinned by `test_sparse_conv_offset_convention_delta_response`.
+  * C helpers (oracle/libgp_oracle.so, built by oracle/Makefile): `knn_ref.c` (OpenMP brute-force
+    kNN, checked against the numpy restatement) and `spmm_ref.c` (OpenMP CSR SpMM, checked BIT FOR
+    BIT against `torch.sparse.mm`, the reference's own pooling call).  They exist so that the
+    full-size parity test (N = 150 000, K = 96, T = 19) and the CPU arm of bench.py run the real
+    workload in seconds; `pool_impl="torch"` keeps the literal `torch.sparse.mm` path.
 """
 from __future__ import annotations
 
