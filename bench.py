@@ -466,14 +466,15 @@ def ours_arm(args):
     for i in range(warm):
         step_resident(i % len(hosts))
     hist.zero_()
+    if args.streams > 1:   # warm the side streams (their arenas) before anything is counted or timed
+        from geopurify_b200.affinity_module import InterleavedScenes
+        inter = InterleavedScenes(model, args.streams)
+        inter.run([resident[i % len(hosts)] for i in range(len(hosts))], hist=hist, ignore=ign, collect=False)
+        torch.cuda.synchronize()
+        hist.zero_()
     l0 = _lib.launch_count
     sampler.mark_begin()
     if args.streams > 1:
-        from geopurify_b200.affinity_module import InterleavedScenes
-        inter = InterleavedScenes(model, args.streams)
-        inter.run([resident[i % len(hosts)] for i in range(len(hosts))], hist=hist, ignore=ign)   # warm the side streams
-        torch.cuda.synchronize()
-        hist.zero_()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
