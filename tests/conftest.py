@@ -29,3 +29,13 @@ def small_scene():
 def small_state():
     from geopurify_b200 import synth
     return synth.make_student_state(input_dim=134, hidden_dim=128, embed_dim=128, seed=3)
+
+
+@pytest.fixture(autouse=True)
+def _workspace_guards(request):
+    """GEOPURIFY_B200_GUARD=1 python -m pytest tests -m gpu: every workspace of every GPU test gets 4 KB canaries on both
+    sides (ops._ws), verified after each test -- the memcheck substitute on a pool where compute-sanitizer is closed."""
+    yield
+    if os.environ.get("GEOPURIFY_B200_GUARD", "0") == "1" and request.node.get_closest_marker("gpu"):
+        from geopurify_b200 import ops
+        ops.check_guards()

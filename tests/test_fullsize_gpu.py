@@ -236,10 +236,11 @@ def test_fullsize_workspace_guard_bands(full_run):
     around every workspace -- the substitute for compute-sanitizer memcheck, which is closed on the build pool."""
     from geopurify_b200 import ops
     r = full_run
+    was = ops._GUARD
     ops.guard_workspaces(True)
     try:
         again = r["model"].run_scene(r["s"], ignore=r["ign"])
         assert ops.check_guards() >= 6
         assert torch.equal(again["labels_voxel"], r["out"]["labels_voxel"])
     finally:
-        ops.guard_workspaces(False)
+        ops.guard_workspaces(was)

@@ -877,6 +877,7 @@ def test_workspace_guard_bands_survive_whole_path(gp, small_scene, small_state):
     from geopurify_b200.affinity_module import SonataXAffinityTrainer, scene_inputs_from_synth
     from geopurify_b200.student import AffinityPredictor, load_numpy_state
     sc = small_scene
+    was = gp._GUARD
     gp.guard_workspaces(True)
     try:
         for lifting in ("mean", "consensus"):
@@ -898,7 +899,7 @@ def test_workspace_guard_bands_survive_whole_path(gp, small_scene, small_state):
         with pytest.raises(Exception, match="guard band"):
             gp.check_guards()
     finally:
-        gp.guard_workspaces(False)
+        gp.guard_workspaces(was)
 
 
 def test_interleaved_scenes_equal_sequential(gp, small_scene, small_state):
