@@ -29,6 +29,10 @@
 #define GP_POOL_DENSE 1   // measured (profiles/r02_*): dense plan 0.233 ms per application at M = 130k, compact 0.272 ms
 #endif
 
+#ifndef GP_POOL_EPI_DIRECT
+#define GP_POOL_EPI_DIRECT 0
+#endif
+
 namespace {
 
 constexpr bool COMPACT = GP_POOL_DENSE == 0;
@@ -410,7 +414,7 @@ __global__ void __launch_bounds__(PTHREADS, 2) pool_tc_kernel(const PoolParams P
   } else if (warp >= 4 && warp < 8) {
     // ===================== epilogue: TMEM -> registers -> 16-column smem transpose -> coalesced rows =====================
     const int q = warp & 3;
-    float* buf = epi + q * 32 * P_EPI_LD;
+    [[maybe_unused]] float* buf = epi + q * 32 * P_EPI_LD;
     uint32_t tcount = 0;
     for (int wi = blockIdx.x; wi < items; wi += gridDim.x) {
       const int t = wi / P.halves, half = wi - t * P.halves;
@@ -419,6 +423,50 @@ __global__ void __launch_bounds__(PTHREADS, 2) pool_tc_kernel(const PoolParams P
       tc::tc_fence_after();
       const int64_t row_base = (int64_t)t * PT + q * 32;
       const int rows_here = (int)min((int64_t)32, P.m - row_base);
+#if GP_POOL_EPI_DIRECT
+      // accumulator-fragment loads (tcgen05.ld.16x256b: four threads hold one 32-byte sector of a row), stored straight
+      // from the registers: no shared-memory transpose, no __syncwarp between TMEM reads, so the accumulator is handed
+      // back to the MMA warp sooner
+#pragma unroll 1
+      for (int hb = 0; hb < 2; ++hb) {
+        const int ra = hb * 16 + (lane >> 2), rb = ra + 8;
+        const bool oka = ra < rows_here, okb = rb < rows_here;
+        const int c0 = half * PH + 2 * (lane & 3);
+#pragma unroll 1
+        for (int cg = 0; cg < PH / 64; ++cg) {
+          uint32_t v[32];
+          tc::tmem_ld_16x256b_x8(tmem_base + ((uint32_t)(q * 32 + hb * 16) << 16) + cg * 64, v);
+          tc::tmem_ld_wait();
+          if (hb == 1 && cg == PH / 64 - 1) {
+            tc::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(tmem_empty);
+          }
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const int col = c0 + cg * 64 + g * 8;
+#pragma unroll
+            for (int r2 = 0; r2 < 2; ++r2) {
+              if (r2 == 0 ? oka : okb) {
+                const int64_t row = row_base + (r2 == 0 ? ra : rb);
+                const float x = __uint_as_float(v[4 * g + 2 * r2]), y = __uint_as_float(v[4 * g + 2 * r2 + 1]);
+                if (P.out_f32) *(float2*)(P.out_f32 + row * P.D + col) = make_float2(x, y);
+                if (P.out_planes) {
+                  __nv_bfloat16 h[2], l[2];
+                  split_bf16(x, h[0], l[0]);
+                  split_bf16(y, h[1], l[1]);
+                  __nv_bfloat16* dst = P.out_planes + row * 2 * P.D + col;
+                  *(uint32_t*)dst = *(const uint32_t*)h;
+                  *(uint32_t*)(dst + P.D) = *(const uint32_t*)l;
+                }
+              }
+            }
+          }
+        }
+      }
+      ++tcount;
+      continue;
+#endif
       for (int ch = 0; ch < PH / 32; ++ch) {
         uint32_t v[32];
         tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ch * 32, v);
