@@ -67,6 +67,7 @@ _SIGS = {
     "gp_scatter_mean_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "gp_scatter_mean_prepare": (c_int, [_P, c_int64, c_int64, _P, c_size_t, _P]),
     "gp_scatter_mean": (c_int, [_P, c_int64, c_int, _P, c_int64, c_int64, _P, c_int64, c_int, _P]),
+    "gp_scatter_mean_static": (c_int, [_P, c_int64, c_int64, _P, c_int64, c_int, _P, c_int64, c_int, _P]),
     "gp_student_workspace_bytes": (c_size_t, [POINTER(StudentDesc), c_int64]),
     "gp_student_forward": (c_int, [POINTER(StudentDesc), _P, _P, c_int64, _P, c_int64, _P, c_int, _P, c_size_t, _P]),
     "gp_student_tc_pack_bytes": (c_size_t, [POINTER(StudentDesc)]),

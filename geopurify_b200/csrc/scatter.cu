@@ -139,3 +139,68 @@ extern "C" int gp_scatter_mean(const float* src, int64_t src_stride, int D, cons
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
+
+// ---- allocation-free variant -------------------------------------------------------------------------------------
+// gp_scatter_mean_static = gp_scatter_mean_prepare + gp_scatter_mean with the scratch (sorted point list, segment
+// offsets, radix-sort keys and CUB's temporary storage) in a file-scope device array instead of a caller workspace,
+// for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No
+// counterpart in the reference.
+//
+// The array is GP_SCATTER_STATIC_BYTES (16 MiB) per GPU that loads the library, held until the process exits.
+// Every call on a device shares it: calls that overlap on the GPU (different streams, or a replay of a captured graph
+// next to a live call) race and must be serialised by the caller.  It keeps the previous call's contents; nothing in
+// it has to start at zero -- the keys, values and the offsets[0..m] are written in full before they are read, and
+// cub::DeviceRadixSort clears its own counters with cudaMemsetAsync on the same stream -- so no clear is issued.
+// Host work: one cudaGetSymbolAddress per device (first call on that device), then kernel launches only: no
+// cudaMalloc / cudaFree / allocating library call (CUB is given its temporary storage).
+static __device__ __align__(256) unsigned char g_scatter_static[GP_SCATTER_STATIC_BYTES];
+
+#define GP_MAX_DEVICES 64
+#include <mutex>
+
+// Device address of g_scatter_static on the CURRENT device.  In host code the symbol's name is only a handle for
+// cudaGetSymbolAddress, never a device pointer.
+static int scatter_static_ptr(void** out) {
+  static std::mutex mu;
+  static void* ptrs[GP_MAX_DEVICES] = {};
+  int dev = -1;
+  GP_CUDA(cudaGetDevice(&dev));
+  GP_CHECK_ARG(dev >= 0 && dev < GP_MAX_DEVICES, "gp_scatter_mean_static: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    GP_CUDA(cudaGetSymbolAddress(&p, g_scatter_static));
+    if (!p) {
+      gp_set_error("gp_scatter_mean_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+      return GP_ERR_CUDA;
+    }
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return GP_OK;
+}
+
+extern "C" int gp_scatter_mean_static(const int32_t* p2v, int64_t n, int64_t m, const float* src, int64_t src_stride,
+                                      int D, float* out, int64_t out_stride, int col0, gp_stream_t stream) {
+  GP_CHECK_ARG(n >= 0 && m >= 0 && D > 0 && src_stride >= D && col0 >= 0 && out_stride >= col0 + D,
+               "gp_scatter_mean_static: bad sizes");
+  if (n > GP_SCATTER_STATIC_MAX_N || m > GP_SCATTER_STATIC_MAX_M) {
+    gp_set_error("gp_scatter_mean_static: n = %lld, m = %lld beyond the static scratch limits (n <= %d, m <= %d); "
+                 "use gp_scatter_mean_prepare + gp_scatter_mean with a caller workspace",
+                 (long long)n, (long long)m, GP_SCATTER_STATIC_MAX_N, GP_SCATTER_STATIC_MAX_M);
+    return GP_ERR_ARG;
+  }
+  ScatterLayout L;
+  scatter_layout(n, m, L);
+  if (L.total > (size_t)GP_SCATTER_STATIC_BYTES) {
+    gp_set_error("gp_scatter_mean_static: scratch for n = %lld, m = %lld is %zu bytes > the %d-byte static array",
+                 (long long)n, (long long)m, L.total, GP_SCATTER_STATIC_BYTES);
+    return GP_ERR_WORKSPACE;
+  }
+  void* scratch = nullptr;
+  int rc = scatter_static_ptr(&scratch);
+  if (rc != GP_OK) return rc;
+  rc = gp_scatter_mean_prepare(p2v, n, m, scratch, (size_t)GP_SCATTER_STATIC_BYTES, stream);
+  if (rc != GP_OK) return rc;
+  return gp_scatter_mean(src, src_stride, D, scratch, n, m, out, out_stride, col0, stream);
+}

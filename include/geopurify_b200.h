@@ -223,6 +223,24 @@ int gp_scatter_mean_prepare(const int32_t* p2v, int64_t n, int64_t m, void* work
 int gp_scatter_mean(const float* src, int64_t src_stride, int D, const void* prepared_workspace, int64_t n,
                     int64_t m, float* out, int64_t out_stride, int col0, gp_stream_t stream);
 
+/* ---- A6 without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and bit-identical result as gp_scatter_mean_prepare + gp_scatter_mean, but the scratch lives in a
+ * 16 MiB `static __device__` array inside the library (held by every GPU that loads it, until process exit) and the
+ * call makes no cudaMalloc / cudaFree / allocating library call.
+ *   limits   n <= GP_SCATTER_STATIC_MAX_N and m <= GP_SCATTER_STATIC_MAX_M, else GP_ERR_ARG with a clear message
+ *            (GP_ERR_WORKSPACE if the layout for (n, m) would still not fit the array);
+ *   sharing  all calls on one GPU use the same array: calls that overlap on the GPU (two streams, or a captured graph
+ *            replayed beside a live call) RACE -- serialise them.  The array keeps the last call's contents; every word
+ *            the call reads it has written first, so there is nothing to clear;
+ *   device   the stream's device must be current (as for every entry point); the first call on a device resolves the
+ *            array's address with cudaGetSymbolAddress, so make that call outside stream capture. */
+#define GP_SCATTER_STATIC_BYTES (16 * 1024 * 1024)
+#define GP_SCATTER_STATIC_MAX_N 262144
+#define GP_SCATTER_STATIC_MAX_M 262144
+int gp_scatter_mean_static(const int32_t* p2v, int64_t n, int64_t m, const float* src, int64_t src_stride, int D,
+                           float* out, int64_t out_stride, int col0, gp_stream_t stream);
+
 /* ---- A8: AffinityPredictor.forward + F.normalize (models/affinity_module.py:33-72, 1546-1547).
  * Sparse 3^3 convolutions as gather-GEMM over the kernel map, BN (eval) + ReLU + residual epilogues.
  *   x        [m, cin_stride] float32 rows in sorted order, cin columns valid
