@@ -29,17 +29,72 @@ constexpr int ROWB = BK * 2;   // bytes per operand row per stage
 #define GP_STU_CL 2
 #endif
 #ifndef GP_STU_NSTAGE
-#define GP_STU_NSTAGE 5
+#define GP_STU_NSTAGE 3
 #define GP_STU_AK 64
 #define GP_STU_NA (GP_STU_CL == 2 ? 4 : 2)
+#endif
+#ifndef GP_STU_UK
+#define GP_STU_UK 4  // K=16 steps per B stage = per barrier hand-off of the MMA issuer: 12 MMAs per wait + fence + commit.
+                     // Measured (student forward, N = 150k scene): UK 1 / 2 / 4 = 11.55 / 11.06 / 10.78 ms
+#endif
+#ifndef GP_STU_EDGE
+#define GP_STU_EDGE 0  // A chunks at each END of a tile's K loop that run as two passes (half 0, then half 1); see for_units.
+                       // 0 = both halves per unit throughout.  Measured: 0 / 2 / 3 chunks = 10.78 / 10.79 / 11.05 ms
 #endif
 #ifndef GP_STU_EPI_DIRECT
 #define GP_STU_EPI_DIRECT 1
 #endif
-constexpr int NSTAGE = GP_STU_NSTAGE;  // B (weight) stages of K=16
+#ifndef GP_STU_PROF
+#define GP_STU_PROF 0  // 1: diagnostic build; CTA 0 prints where its MMA issuer, epilogue warp 4 and gather warp 8 waited
+#endif
+#if GP_STU_PROF
+#define PROF_T0() const long long pt0_ = clock64()
+#define PROF_ADD(acc) acc += clock64() - pt0_
+#else
+#define PROF_T0()
+#define PROF_ADD(acc)
+#endif
+#ifndef GP_STU_ABLATE
+#define GP_STU_ABLATE 0  // 1 / 2: diagnostic builds (wrong results) whose epilogue skips the stores / the TMEM loads too
+#endif
+constexpr int NSTAGE = GP_STU_NSTAGE;  // B (weight) stages: UK K-steps of ONE column half (<= 256 outputs), hi + lo planes
+constexpr int UK = GP_STU_UK;          // K=16 steps per stage (a divisor of AKS, so a stage never straddles an A chunk)
 constexpr int AK = GP_STU_AK;  // K per A chunk: 64- or 128-byte operand rows, SWIZZLE_64B / SWIZZLE_128B
 constexpr int AKS = AK / BK;   // K=16 steps per A chunk
 constexpr int NA = GP_STU_NA;  // A chunk buffers
+constexpr int EDGE = GP_STU_EDGE < NA - 1 ? GP_STU_EDGE : NA - 2;  // an edge block keeps <= EDGE + 1 chunks resident and
+                                                                   // one more buffer stays free for the gather's lag
+
+// Order of the (column half h, K-steps) units of one tile, shared by the TMA producer and the MMA issuer.
+// N <= 256 (NH = 1): K ascending.  N = 512 (NH = 2 halves of 256 columns, each with its own full/empty barriers):
+//   EDGE = 0 (default): both halves per unit position, K ascending -- the two accumulators alternate every unit;
+//   EDGE > 0 (build option): the first EDGE chunks run as two passes (all their K-steps into half 0, then the same,
+//   still resident, A chunks into half 1), the middle alternates, the last EDGE chunks run as two passes again, so
+//   that half 0 is complete one pass before half 1 and drains under half 1's last pass, and half 1 drains under the
+//   next tile's first pass.  Why it exists: an SM stores at most 32 B/clk (scripts/probes/store_bw.cu; ~17 B/clk inside
+//   this kernel, where the gathers share the path), so draining a 128 x 512 fp32 accumulator takes 8-15k clk of a
+//   ~40k-clk tile and the tensor pipe idles meanwhile (builds without the stores: -2.1 ms of a 10.9 ms forward).  Why it
+//   is off: hiding a 7.5k-clk half drain needs passes of >= 4 chunks, i.e. >= 6 resident A buffers (192 KB) -- with the
+//   2-3 chunks that fit, the issuer still waits ~9k clk per tile on tmem_empty (GP_STU_PROF=1) and nothing is gained.
+// A unit is UK consecutive K-steps (the last one of a tile may be shorter): f(h, first K-step, number of K-steps).
+template <int NH, typename F>
+__device__ __forceinline__ void for_units(int ksteps, F&& f) {
+  static_assert(AKS % UK == 0, "a B stage must not straddle an A chunk");
+  auto nk = [&](int ks, int end) { return end - ks < UK ? end - ks : UK; };
+  if (NH == 1 || EDGE <= 0) {
+    for (int ks = 0; ks < ksteps; ks += UK)
+      for (int h = 0; h < NH; ++h) f(h, ks, nk(ks, ksteps));
+    return;
+  }
+  int ka = EDGE * AKS < ksteps ? EDGE * AKS : ksteps;                       // end of the first edge block
+  int kb = ksteps - EDGE * AKS > ka ? (ksteps - EDGE * AKS) / AKS * AKS : ka;  // start of the last one (chunk-aligned)
+  for (int h = 0; h < NH; ++h)
+    for (int ks = 0; ks < ka; ks += UK) f(h, ks, nk(ks, ka));
+  for (int ks = ka; ks < kb; ks += UK)
+    for (int h = 0; h < NH; ++h) f(h, ks, nk(ks, kb));
+  for (int h = 0; h < NH; ++h)
+    for (int ks = kb; ks < ksteps; ks += UK) f(h, ks, nk(ks, ksteps));
+}
 constexpr int CL = GP_STU_CL;  // 2: CTA pairs (cta_group::2).  Two tiles of one kernel offset form one M = 256 MMA over
                                // two SMs; each SM gathers its own 128 A rows and ingests only HALF of every W_o slice
 constexpr bool PAIR = CL == 2;
@@ -56,16 +111,22 @@ struct TileInfo {  // one 128-pair tile
 
 template <int N>
 struct Smem {
+  static constexpr int UN = N < 256 ? N : 256;      // UMMA N = columns of one accumulator
+  static constexpr int NH = N / UN;                 // column halves per tile (2 for N = 512)
+  static constexpr int TCOLS = NH == 2 ? N : 2 * N; // TMEM columns: two halves, or two alternating accumulators
   static constexpr int A_BYTES = TM * AK * 2;       // per plane per chunk (16 KB)
   static constexpr int A_CHUNK = 2 * A_BYTES;       // hi + lo
-  static constexpr int B_BYTES = (PAIR ? N / 2 : N) * ROWB;  // per plane (a CTA of a pair holds half of the rows)
-  static constexpr int STAGE = 2 * B_BYTES;
+  static constexpr int B_BYTES = (PAIR ? UN / 2 : UN) * ROWB;  // per plane per K-step (a CTA of a pair holds half of the rows)
+  static constexpr int STAGE = UK * 2 * B_BYTES;               // [K-step][plane][rows][16]
   static constexpr int A_OFF = 0;
   static constexpr int B_OFF = NA * A_CHUNK;
   static constexpr int EPI_OFF = B_OFF + NSTAGE * STAGE;
-  static constexpr int EPI = 4 * 32 * EPI_LD * 4;
+  static constexpr int EPI = GP_STU_EPI_DIRECT ? 0 : 4 * 32 * EPI_LD * 4;  // transpose buffer (non-direct epilogue only)
   static constexpr int BAR_OFF = EPI_OFF + EPI;
-  static constexpr int TOTAL = BAR_OFF + 256;         // + barriers
+  static constexpr int TOTAL = BAR_OFF + 512;       // + barriers and the TMEM slot
+  static_assert((2 * NSTAGE + 2 * NA + 4) * 8 + 4 <= 512, "barrier block too small");
+  static_assert(TOTAL <= 232448, "more shared memory than a CTA can have");
+  static_assert(TCOLS <= 512, "TMEM has 512 columns");
 };
 
 struct GemmParams {
@@ -100,9 +161,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
   uint64_t* b_empty = b_full + NSTAGE;       // [NSTAGE] MMAs reading the stage have completed
   uint64_t* a_full = b_empty + NSTAGE;       // [NA] A chunk gathered (4 gather warps)
   uint64_t* a_empty = a_full + NA;           // [NA] MMAs reading the chunk have completed
-  uint64_t* tmem_full = a_empty + NA;        // accumulator complete
-  uint64_t* tmem_empty = tmem_full + 1;      // accumulator drained
-  uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 1);
+  uint64_t* tmem_full = a_empty + NA;        // [2] accumulator (half) complete
+  uint64_t* tmem_empty = tmem_full + 2;      // [2] accumulator (half) drained
+  uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 2);
+  // TMEM holds two accumulators of UN <= 256 columns.  N = 512: the two column halves of one tile, each with its own
+  // full/empty barrier pair, so that a half drains while the MMAs run on the other one (below).  N <= 256: two whole
+  // accumulators used by alternate tiles.
+  constexpr int UN = S::UN, NH = S::NH;
+  auto part_bar = [&](uint32_t tcount, int h) -> int { return NH == 2 ? h : (int)(tcount & 1); };
+  auto part_phase = [&](uint32_t tcount) -> uint32_t { return NH == 2 ? (tcount & 1) : ((tcount >> 1) & 1); };
+  auto part_col = [&](uint32_t tcount, int h) -> uint32_t { return NH == 2 ? h * UN : (tcount & 1) * N; };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ntiles_real = P.ntiles_dev ? *P.ntiles_dev : P.ntiles_host;
@@ -123,13 +191,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
       tc::mbar_init(&a_full[s], PAIR ? 8 : 4);  // pair: the leader's barrier collects both CTAs' gather warps
       tc::mbar_init(&a_empty[s], 1);
     }
-    tc::mbar_init(tmem_full, 1);
-    tc::mbar_init(tmem_empty, PAIR ? 8 : 4);
+    for (int s = 0; s < 2; ++s) {
+      tc::mbar_init(&tmem_full[s], 1);
+      tc::mbar_init(&tmem_empty[s], PAIR ? 8 : 4);
+    }
     tc::fence_barrier_init();
   }
   if (warp == 2) {
-    if (PAIR) tc::tmem_alloc2<N>(tmem_slot);
-    else tc::tmem_alloc<N>(tmem_slot);
+    if (PAIR) tc::tmem_alloc2<S::TCOLS>(tmem_slot);
+    else tc::tmem_alloc<S::TCOLS>(tmem_slot);
   }
   tc::tc_fence_before();
   __syncthreads();
@@ -153,208 +223,232 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
   };
 
   if (warp == 0) {
-    // ===================== TMA producer: W_o^T[k0:k0+16] hi + lo for all N outputs =====================
+    // ===================== TMA producer: W_o^T[k0:k0+16] hi + lo of ONE column half per stage =====================
+    // stage order = the MMA issuer's: K-blocks of KBS steps, inside a block first half 0 then half 1
     if (lane == 0) {
       uint32_t it = 0;
-      [[maybe_unused]] constexpr int BOX = N < 256 ? N : 256;
       for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
         const TileInfo ti = tile_of(t);
-        for (int ks = 0; ks < ksteps; ++ks, ++it) {
+        for_units<NH>(ksteps, [&](int h, int ks, int nk) {
           const int s = it % NSTAGE;
           const uint32_t ph = (it / NSTAGE) & 1;
+          ++it;
           tc::mbar_wait(&b_empty[s], ph ^ 1);
           uint8_t* st = smem + S::B_OFF + s * S::STAGE;
-          if constexpr (PAIR) {
-            // leader: expect both CTAs' halves; every CTA fetches the N/2 rows it feeds to each N = UN instruction
-            constexpr int UNP = N < 256 ? N : 256, HALF = UNP / 2;
-            if (crank == 0) tc::mbar_arrive_expect_tx(&b_full[s], 2 * S::STAGE);
+          // leader of a pair: expect both CTAs' halves; every CTA fetches the UN/2 rows it feeds to the M = 256 instruction
+          if (!PAIR || crank == 0) tc::mbar_arrive_expect_tx(&b_full[s], (PAIR ? 2 : 1) * nk * 2 * S::B_BYTES);
+          for (int j = 0; j < nk; ++j) {
+            const int row0 = (ti.offset * 2 * ksteps + ks + j) * P.cout_total + h * UN;  // plane 0; plane 1: ksteps blocks on
 #pragma unroll
-            for (int plane = 0; plane < 2; ++plane)
-#pragma unroll
-              for (int h = 0; h < N / UNP; ++h)
-                tc::tma_load_2d_2sm(tc::smem_u32(st + plane * S::B_BYTES + h * HALF * ROWB), &wmap, 0,
-                                    ((ti.offset * 2 + plane) * ksteps + ks) * P.cout_total + h * UNP + (int)crank * HALF,
-                                    &b_full[s]);
-          } else {
-            tc::mbar_arrive_expect_tx(&b_full[s], 2 * S::B_BYTES);
-#pragma unroll
-            for (int plane = 0; plane < 2; ++plane)
-#pragma unroll
-              for (int nb = 0; nb < N / BOX; ++nb)
-                tc::tma_load_2d(tc::smem_u32(st + plane * S::B_BYTES + nb * BOX * ROWB), &wmap, 0,
-                                ((ti.offset * 2 + plane) * ksteps + ks) * P.cout_total + nb * BOX, &b_full[s]);
+            for (int plane = 0; plane < 2; ++plane) {
+              const uint32_t dst = tc::smem_u32(st + (j * 2 + plane) * S::B_BYTES);
+              if constexpr (PAIR)
+                tc::tma_load_2d_2sm(dst, &wmap, 0, row0 + plane * ksteps * P.cout_total + (int)crank * (UN / 2), &b_full[s]);
+              else
+                tc::tma_load_2d(dst, &wmap, 0, row0 + plane * ksteps * P.cout_total, &b_full[s]);
+            }
           }
-        }
+        });
       }
     }
   } else if (warp == 1 && (!PAIR || crank == 0)) {
     // ===================== MMA issuer (pair mode: the leader CTA issues for both SMs) =====================
+    // unit order: for_units above.  Every unit is three MMAs (M = 128 or 256 over the pair, N = UN, K = 16) into the
+    // unit's accumulator; a chunk buffer is released after its last K-step in the LAST half that reads it.
     constexpr uint64_t DB = tc::umma_desc_kmajor_base<ROWB>();
     constexpr uint64_t DA = tc::umma_desc_kmajor_base<AK * 2>();
-    constexpr int UN = N < 256 ? N : 256;
     constexpr uint32_t IDESC = tc::umma_idesc_bf16(PAIR ? 2 * TM : TM, UN);
     uint32_t it = 0, ac = 0, tcount = 0;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
-      tc::mbar_wait(tmem_empty, (tcount & 1) ^ 1);
-      tc::tc_fence_after();
-      for (int ks = 0; ks < ksteps; ++ks, ++it) {
+    [[maybe_unused]] long long w_te = 0, w_af = 0, w_bf = 0;
+    [[maybe_unused]] const long long prof_start = clock64();
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount, ac += nchunks) {
+      for_units<NH>(ksteps, [&](int h, int ks, int nk) {
+        const int pb = part_bar(tcount, h);
+        if (ks == 0) {  // first unit of this half in the tile: the previous contents must have been drained
+          PROF_T0();
+          tc::mbar_wait(&tmem_empty[pb], part_phase(tcount) ^ 1);
+          PROF_ADD(w_te);
+        }
+        const uint32_t d = tmem_base + part_col(tcount, h);
         const int s = it % NSTAGE;
         const uint32_t ph = (it / NSTAGE) & 1;
-        const int ab = ac % NA;
-        if ((ks & (AKS - 1)) == 0) tc::mbar_wait(&a_full[ab], (ac / NA) & 1);
-        tc::mbar_wait(&b_full[s], ph);
+        ++it;
+        const uint32_t aci = ac + ks / AKS;  // running index of this tile's chunk (a unit never straddles chunks)
+        const int ab = aci % NA;
+        if (h == 0 && (ks & (AKS - 1)) == 0) {
+          PROF_T0();
+          tc::mbar_wait(&a_full[ab], (aci / NA) & 1);
+          PROF_ADD(w_af);
+        }
+        {
+          PROF_T0();
+          tc::mbar_wait(&b_full[s], ph);
+          PROF_ADD(w_bf);
+        }
         tc::tc_fence_after();
-        const bool chunk_end = (ks & (AKS - 1)) == AKS - 1 || ks == ksteps - 1;
+        const int kl = ks + nk - 1;  // last K-step of the unit
+        const bool chunk_end = (kl & (AKS - 1)) == AKS - 1 || kl == ksteps - 1;
         if (lane == 0) {
-          // K=16 slice j of a 128-byte swizzled row starts 32 j bytes into the (1024-byte aligned) tile
-          const uint32_t a_hi = tc::smem_u32(smem + S::A_OFF + ab * S::A_CHUNK) + (ks & (AKS - 1)) * ROWB;
-          const uint32_t a_lo = a_hi + S::A_BYTES;
-          const uint32_t b_hi = tc::smem_u32(smem + S::B_OFF + s * S::STAGE);
-          const uint32_t b_lo = b_hi + S::B_BYTES;
-#pragma unroll
-          for (int h = 0; h < N / UN; ++h) {
-            const uint32_t d = tmem_base + h * UN;
-            const uint32_t boff = h * (PAIR ? UN / 2 : UN) * ROWB;
+          for (int j = 0; j < nk; ++j) {
+            // K=16 slice j of a 128-byte swizzled row starts 32 j bytes into the (1024-byte aligned) tile
+            const uint32_t a_hi = tc::smem_u32(smem + S::A_OFF + ab * S::A_CHUNK) + ((ks + j) & (AKS - 1)) * ROWB;
+            const uint32_t a_lo = a_hi + S::A_BYTES;
+            const uint32_t b_hi = tc::smem_u32(smem + S::B_OFF + s * S::STAGE) + j * 2 * S::B_BYTES;
+            const uint32_t b_lo = b_hi + S::B_BYTES;
             // small terms first, then the leading product
             if constexpr (PAIR) {
-              tc::umma_bf16_2sm(d, tc::umma_desc(DA, a_lo), tc::umma_desc(DB, b_hi + boff), IDESC, ks > 0);
-              tc::umma_bf16_2sm(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_lo + boff), IDESC, 1);
-              tc::umma_bf16_2sm(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_hi + boff), IDESC, 1);
+              tc::umma_bf16_2sm(d, tc::umma_desc(DA, a_lo), tc::umma_desc(DB, b_hi), IDESC, ks + j > 0);
+              tc::umma_bf16_2sm(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_lo), IDESC, 1);
+              tc::umma_bf16_2sm(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_hi), IDESC, 1);
             } else {
-              tc::umma_bf16(d, tc::umma_desc(DA, a_lo), tc::umma_desc(DB, b_hi + boff), IDESC, ks > 0);
-              tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_lo + boff), IDESC, 1);
-              tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_hi + boff), IDESC, 1);
+              tc::umma_bf16(d, tc::umma_desc(DA, a_lo), tc::umma_desc(DB, b_hi), IDESC, ks + j > 0);
+              tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_lo), IDESC, 1);
+              tc::umma_bf16(d, tc::umma_desc(DA, a_hi), tc::umma_desc(DB, b_hi), IDESC, 1);
             }
           }
           if constexpr (PAIR) {  // the same barrier offset in both CTAs
             tc::umma_commit_2sm(&b_empty[s], CMASK);
-            if (chunk_end) tc::umma_commit_2sm(&a_empty[ab], CMASK);
-            if (ks == ksteps - 1) tc::umma_commit_2sm(tmem_full, CMASK);
+            if (h == NH - 1 && chunk_end) tc::umma_commit_2sm(&a_empty[ab], CMASK);
+            if (kl == ksteps - 1) tc::umma_commit_2sm(&tmem_full[pb], CMASK);
           } else {
             tc::umma_commit(&b_empty[s]);
-            if (chunk_end) tc::umma_commit(&a_empty[ab]);
-            if (ks == ksteps - 1) tc::umma_commit(tmem_full);
+            if (h == NH - 1 && chunk_end) tc::umma_commit(&a_empty[ab]);
+            if (kl == ksteps - 1) tc::umma_commit(&tmem_full[pb]);
           }
         }
         __syncwarp();
-        if (chunk_end) ++ac;
-      }
+      });
     }
+#if GP_STU_PROF
+    if (blockIdx.x == 0 && lane == 0 && N == 512)
+      printf("PROF mma: total %lld clk, tiles %u, wait tmem_empty %lld a_full %lld b_full %lld\n", clock64() - prof_start,
+             tcount, w_te, w_af, w_bf);
+#endif
   } else if (warp >= 4 && warp < 8) {
-    // ===================== epilogue: TMEM -> registers -> smem transpose -> coalesced global rows =====================
+    // ===================== epilogue: TMEM -> registers -> global rows, one accumulator (half) at a time ==============
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
     [[maybe_unused]] float* buf = epi + q * 32 * EPI_LD;
     uint32_t tcount = 0;
+    [[maybe_unused]] long long w_tf = 0;
+    [[maybe_unused]] const long long prof_start = clock64();
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
       const TileInfo ti = tile_of(t);
-      tc::mbar_wait(tmem_full, tcount & 1);
-      tc::tc_fence_after();
       const int rows_here = ti.nrows - q * 32;  // valid rows in this warp's quadrant
-      if (P.label_out) {
-        // classification: thread = accumulator row, so the arg-max over the columns is thread-local -- no transpose,
-        // no logits in HBM.  Strict > in ascending column order keeps the lowest class index on ties.
-        float best = -INFINITY, second = -INFINITY;
-        int besti = 0;
-        const int nch = (P.ncols + 31) / 32;
-        for (int ch = 0; ch < N / 32; ++ch) {
-          if (ch < nch) {
-            uint32_t v[32];
-            tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ch * 32, v);
-            tc::tmem_ld_wait();
+      for (int h = 0; h < NH; ++h) {
+        const int pb = part_bar(tcount, h);
+        const uint32_t tacc = tmem_base + part_col(tcount, h);
+        {
+          PROF_T0();
+          tc::mbar_wait(&tmem_full[pb], part_phase(tcount));
+          PROF_ADD(w_tf);
+        }
+        tc::tc_fence_after();
+        auto release = [&]() {  // this warp has read its quadrant of the accumulator: the MMAs may overwrite it
+          tc::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (PAIR && crank != 0) tc::mbar_arrive_cluster(&tmem_empty[pb], 0);
+            else tc::mbar_arrive(&tmem_empty[pb]);
+          }
+        };
+        if (P.label_out) {
+          // classification (N <= 256, one accumulator per tile): thread = accumulator row, so the arg-max over the
+          // columns is thread-local -- no transpose, no logits in HBM.  Strict > in ascending column order keeps the
+          // lowest class index on ties.
+          float best = -INFINITY, second = -INFINITY;
+          int besti = 0;
+          const int nch = (P.ncols + 31) / 32;
+          for (int ch = 0; ch < UN / 32; ++ch) {
+            if (ch < nch) {
+              uint32_t v[32];
+              tc::tmem_ld32(tacc + ((uint32_t)(q * 32) << 16) + ch * 32, v);
+              tc::tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float x = __uint_as_float(v[j]);
-              if (ch * 32 + j < P.ncols) {
-                if (x > best) {
-                  second = best;
-                  best = x;
-                  besti = ch * 32 + j;
-                } else if (x > second) {
-                  second = x;
+              for (int j = 0; j < 32; ++j) {
+                const float x = __uint_as_float(v[j]);
+                if (ch * 32 + j < P.ncols) {
+                  if (x > best) {
+                    second = best;
+                    best = x;
+                    besti = ch * 32 + j;
+                  } else if (x > second) {
+                    second = x;
+                  }
                 }
               }
             }
           }
-          if (ch == N / 32 - 1) {
-            tc::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) {
-              if (PAIR && crank != 0) tc::mbar_arrive_cluster(tmem_empty, 0);
-              else tc::mbar_arrive(tmem_empty);
-            }
+          release();
+          if (lane < rows_here) {
+            const int64_t row = (int64_t)ti.c_row0 + q * 32 + lane;
+            P.label_out[row] = besti;
+            // !(a > b) also catches NaN accumulators and all-zero rows (margin 0, norm 0)
+            P.flag_out[row] = !((best - second) > P.margin_rel * __ldg(P.rnorm + row)) || !(best > -INFINITY);
           }
+          continue;
         }
-        if (lane < rows_here) {
-          const int64_t row = (int64_t)ti.c_row0 + q * 32 + lane;
-          P.label_out[row] = besti;
-          // !(a > b) also catches NaN accumulators and all-zero rows (margin 0, norm 0)
-          P.flag_out[row] = !((best - second) > P.margin_rel * __ldg(P.rnorm + row)) || !(best > -INFINITY);
-        }
+#if GP_STU_ABLATE == 2
+        release();
         continue;
-      }
-      float* crow = P.c + ((int64_t)ti.c_row0 + q * 32) * P.ldc;
+#endif
+        float* crow = P.c + ((int64_t)ti.c_row0 + q * 32) * P.ldc + h * UN;
 #if GP_STU_EPI_DIRECT
-      // accumulator-fragment loads: four threads hold one 32-byte sector of a row, stored as float2 straight from the
-      // registers -- no shared-memory transpose (the smem port is shared with the MMAs' operand reads)
+        // accumulator-fragment loads: four threads hold one 32-byte sector of a row, stored as float2 straight from
+        // the registers -- no shared-memory transpose (the smem port is shared with the MMAs' operand reads)
 #pragma unroll 1
-      for (int hb = 0; hb < 2; ++hb) {
-        const int ra = hb * 16 + (lane >> 2), rb = ra + 8;
-        float* pa = crow + (int64_t)ra * P.ldc + 2 * (lane & 3);
-        float* pb = crow + (int64_t)rb * P.ldc + 2 * (lane & 3);
+        for (int hb = 0; hb < 2; ++hb) {
+          const int ra = hb * 16 + (lane >> 2), rb = ra + 8;
+          float* pa = crow + (int64_t)ra * P.ldc + 2 * (lane & 3);
+          float* pb2 = crow + (int64_t)rb * P.ldc + 2 * (lane & 3);
 #pragma unroll 1
-        for (int cg = 0; cg < N / 64; ++cg) {
-          uint32_t v[32];
-          tc::tmem_ld_16x256b_x8(tmem_base + ((uint32_t)(q * 32 + hb * 16) << 16) + cg * 64, v);
-          tc::tmem_ld_wait();
-          if (hb == 1 && cg == N / 64 - 1) {  // accumulator fully read: the next tile's MMAs may start
-            tc::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) {
-              if (PAIR && crank != 0) tc::mbar_arrive_cluster(tmem_empty, 0);
-              else tc::mbar_arrive(tmem_empty);
+          for (int cg = 0; cg < UN / 64; ++cg) {
+            uint32_t v[32];
+            tc::tmem_ld_16x256b_x8(tacc + ((uint32_t)(q * 32 + hb * 16) << 16) + cg * 64, v);
+            tc::tmem_ld_wait();
+            if (hb == 1 && cg == UN / 64 - 1) release();
+#if GP_STU_ABLATE == 1
+            if (v[0] == 0x7fc12345u && v[31] == 0x7fc54321u) pa[0] = 1.f;
+            continue;
+#endif
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+              const int col = cg * 64 + g * 8;
+              if (ra < rows_here)
+                *(float2*)(pa + col) = make_float2(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]));
+              if (rb < rows_here)
+                *(float2*)(pb2 + col) = make_float2(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
             }
           }
-#pragma unroll
-          for (int g = 0; g < 8; ++g) {
-            const int col = cg * 64 + g * 8;
-            if (ra < rows_here)
-              *(float2*)(pa + col) = make_float2(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]));
-            if (rb < rows_here)
-              *(float2*)(pb + col) = make_float2(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
-          }
         }
-      }
 #else
-      for (int ch = 0; ch < N / 32; ++ch) {
-        uint32_t v[32];
-        tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ch * 32, v);
-        tc::tmem_ld_wait();
-        if (ch == N / 32 - 1) {  // accumulator fully read: the next tile's MMAs may start
-          tc::tc_fence_before();
+        for (int ch = 0; ch < UN / 32; ++ch) {
+          uint32_t v[32];
+          tc::tmem_ld32(tacc + ((uint32_t)(q * 32) << 16) + ch * 32, v);
+          tc::tmem_ld_wait();
+          if (ch == UN / 32 - 1) release();
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *(float4*)(buf + lane * EPI_LD + j * 4) =
+                make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                            __uint_as_float(v[4 * j + 3]));
           __syncwarp();
-          if (lane == 0) {
-            if (PAIR && crank != 0) tc::mbar_arrive_cluster(tmem_empty, 0);
-            else tc::mbar_arrive(tmem_empty);
-          }
-        }
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *(float4*)(buf + lane * EPI_LD + j * 4) =
-              make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
-                          __uint_as_float(v[4 * j + 3]));
-        __syncwarp();
-#pragma unroll
-        for (int rr = 0; rr < 8; ++rr) {
-          const int row = rr * 4 + (lane >> 3), c4 = lane & 7;
-          if (row < rows_here) {
-            float4 o = *(const float4*)(buf + row * EPI_LD + c4 * 4);
-            *(float4*)(crow + (int64_t)row * P.ldc + ch * 32 + c4 * 4) = o;
+          for (int rr = 0; rr < 8; ++rr) {
+            const int row = rr * 4 + (lane >> 3), c4 = lane & 7;
+            if (row < rows_here) {
+              float4 o = *(const float4*)(buf + row * EPI_LD + c4 * 4);
+              *(float4*)(crow + (int64_t)row * P.ldc + ch * 32 + c4 * 4) = o;
+            }
           }
+          __syncwarp();
         }
-        __syncwarp();
-      }
 #endif
+      }
     }
+#if GP_STU_PROF
+    if (blockIdx.x == 0 && threadIdx.x == 128 && N == 512)
+      printf("PROF epi: total %lld clk, wait tmem_full %lld (the rest is draining)\n", clock64() - prof_start, w_tf);
+#endif
   } else if (warp >= 8) {
     // ===================== A gather: warp w owns tile rows [32 w, 32 w + 32); 8 lanes fetch one 128-byte row slice ====
     const int w = warp - 8;
@@ -362,6 +456,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
     constexpr int RPI = 32 / LPR;      // rows per warp-wide cp.async
     const int rsub = lane / LPR, c = lane % LPR;
     uint32_t ac = 0, signalled = 0;
+    [[maybe_unused]] long long w_ae = 0, w_land = 0;
+    [[maybe_unused]] const long long prof_start = clock64();
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
       const TileInfo ti = tile_of(t);
       const int r = w * 32 + lane;
@@ -369,7 +465,23 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
       if (r < ti.nrows) my_row = P.pair_in ? __ldg(P.pair_in + ti.p0 + r) : ti.p0 + r;
       for (int ci = 0; ci < nchunks; ++ci, ++ac) {
         const int ab = ac % NA;
-        tc::mbar_wait(&a_empty[ab], ((ac / NA) & 1) ^ 1);
+        if (signalled < ac && !__all_sync(0xffffffffu, tc::mbar_test(&a_empty[ab], ((ac / NA) & 1) ^ 1))) {
+          // about to block on a buffer the MMAs still read: hand over the chunk already issued first (the issuer may be
+          // waiting for exactly that chunk before it can release this buffer)
+          tc::cp_async_wait<0>();
+          tc::fence_proxy_async();
+          __syncwarp();
+          for (; signalled < ac; ++signalled)
+            if (lane == 0) {
+              if (PAIR && crank != 0) tc::mbar_arrive_cluster(&a_full[signalled % NA], 0);
+              else tc::mbar_arrive(&a_full[signalled % NA]);
+            }
+        }
+        {
+          PROF_T0();
+          tc::mbar_wait(&a_empty[ab], ((ac / NA) & 1) ^ 1);
+          PROF_ADD(w_ae);
+        }
         const int kvalid = min(AK, P.kp - ci * AK);  // elements of this chunk that exist
         const uint32_t abase = tc::smem_u32(smem + S::A_OFF + ab * S::A_CHUNK);
 #pragma unroll
@@ -385,7 +497,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
         }
         tc::cp_async_commit();
         if (ac >= ALAG) {  // the chunk issued ALAG iterations ago has landed
+          PROF_T0();
           tc::cp_async_wait<ALAG>();
+          PROF_ADD(w_land);
           tc::fence_proxy_async();
           __syncwarp();
           if (lane == 0) {
@@ -404,14 +518,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
         if (PAIR && crank != 0) tc::mbar_arrive_cluster(&a_full[signalled % NA], 0);
         else tc::mbar_arrive(&a_full[signalled % NA]);
       }
+#if GP_STU_PROF
+    if (blockIdx.x == 0 && threadIdx.x == 256 && N == 512)
+      printf("PROF gather: total %lld clk, chunks %u, wait a_empty %lld, wait landing %lld\n", clock64() - prof_start, ac,
+             w_ae, w_land);
+#endif
   }
 
   tc::tc_fence_before();
   __syncthreads();
   if (CL > 1) tc::cluster_sync_all();  // no CTA leaves while its peer may still signal it or read its smem
   if (warp == 2) {
-    if (PAIR) tc::tmem_dealloc2<N>(tmem_base);
-    else tc::tmem_dealloc<N>(tmem_base);
+    if (PAIR) tc::tmem_dealloc2<S::TCOLS>(tmem_base);
+    else tc::tmem_dealloc<S::TCOLS>(tmem_base);
   }
 }
 

@@ -1,0 +1,87 @@
+// Calibration probe (not product): how fast can ONE SM push a 128 x 512 fp32 tile (256 KB, rows contiguous) to global
+// memory, as a function of the per-instruction store pattern and the number of storing warps?  The student GEMM's
+// epilogue drains such a tile from TMEM while the tensor pipe waits (the accumulator fills TMEM, so it cannot be
+// double-buffered); the `GP_STU_ABLATE` builds put the cost of the stores at ~2.1 ms of a 10.9 ms forward.
+// One CTA per SM, each CTA writes its own sequence of tiles.  Patterns (rows x bytes per warp instruction):
+//   0: 8 rows x 32 B  (STG.64, four lanes per sector -- the tcgen05.ld.16x256b fragment stored as is)
+//   1: 8 rows x 64 B  (STG.128, a quad writes 64 contiguous bytes)
+//   2: 4 rows x 128 B (STG.128, eight lanes per row -- the round-1 smem-transposed epilogue)
+//   3: 2 rows x 256 B (STG.128)
+//   4: 1 row  x 512 B (STG.128, fully coalesced)
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o scripts/probes/store_bw scripts/probes/store_bw.cu
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+constexpr int ROWS = 128, COLS = 512;
+
+template <int PAT>
+__global__ void __launch_bounds__(256) store_kernel(float* out, int tiles_per_cta, long long* clk) {
+  const int nwarps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = warp & 3;                                  // row quadrant, as the TMEM lane restriction forces
+  const int chalf = warp >> 2, ncol = COLS / (nwarps / 4); // 8 warps: second set takes the upper column half
+  const float v = (float)threadIdx.x;
+  __syncthreads();
+  const long long t0 = clock64();
+  for (int t = 0; t < tiles_per_cta; ++t) {
+    float* tile = out + ((size_t)blockIdx.x * tiles_per_cta + t) * ROWS * COLS + (size_t)q * 32 * COLS + chalf * ncol;
+    if (PAT == 0) {
+      for (int hb = 0; hb < 2; ++hb)
+        for (int c0 = 0; c0 < ncol; c0 += 8) {
+          float* p = tile + (size_t)(hb * 16 + (lane >> 2)) * COLS + c0 + 2 * (lane & 3);
+          *(float2*)p = make_float2(v, v);
+          *(float2*)(p + 8 * COLS) = make_float2(v, v);
+        }
+    } else {
+      constexpr int LPR = PAT == 1 ? 4 : PAT == 2 ? 8 : PAT == 3 ? 16 : 32;  // lanes per row
+      constexpr int RPI = 32 / LPR;                                           // rows per instruction
+      for (int r0 = 0; r0 < 32; r0 += RPI)
+        for (int c0 = 0; c0 < ncol; c0 += LPR * 4) {
+          float* p = tile + (size_t)(r0 + lane / LPR) * COLS + c0 + (lane % LPR) * 4;
+          *(float4*)p = make_float4(v, v, v, v);
+        }
+    }
+  }
+  __syncthreads();
+  const long long t1 = clock64();
+  if (threadIdx.x == 0) clk[blockIdx.x] = t1 - t0;
+}
+
+template <int PAT>
+void run(float* buf, long long* clk, int grid, int threads, int tiles) {
+  store_kernel<PAT><<<grid, threads>>>(buf, tiles, clk);  // warm-up
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  cudaEventRecord(e0);
+  store_kernel<PAT><<<grid, threads>>>(buf, tiles, clk);
+  cudaEventRecord(e1);
+  cudaDeviceSynchronize();
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  long long h[256], mx = 0;
+  cudaMemcpy(h, clk, sizeof(long long) * grid, cudaMemcpyDeviceToHost);
+  for (int i = 0; i < grid; ++i) mx = h[i] > mx ? h[i] : mx;
+  const double bytes = (double)tiles * ROWS * COLS * 4;
+  printf("pattern %d  warps %d  grid %3d : %7.1f B/clk/SM  (%.0f clk per 256 KB tile)  aggregate %6.0f GB/s  err=%s\n", PAT,
+         threads / 32, grid, bytes / (double)mx, (double)mx / tiles, bytes * grid / ms / 1e6,
+         cudaGetErrorString(cudaGetLastError()));
+}
+
+int main() {
+  const int tiles = 32;  // 8 MB per CTA, 1.2 GB in all: far beyond L2, like the staging buffer
+  float* buf;
+  long long* clk;
+  cudaMalloc(&buf, (size_t)148 * tiles * ROWS * COLS * 4);
+  cudaMalloc(&clk, 256 * sizeof(long long));
+  for (int grid : {148, 1}) {
+    for (int threads : {128, 256}) {
+      run<0>(buf, clk, grid, threads, tiles);
+      run<1>(buf, clk, grid, threads, tiles);
+      run<2>(buf, clk, grid, threads, tiles);
+      run<3>(buf, clk, grid, threads, tiles);
+      run<4>(buf, clk, grid, threads, tiles);
+    }
+  }
+  return 0;
+}
