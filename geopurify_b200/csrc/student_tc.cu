@@ -62,8 +62,9 @@ constexpr int UK = GP_STU_UK;          // K=16 steps per stage (a divisor of AKS
 constexpr int AK = GP_STU_AK;  // K per A chunk: 64- or 128-byte operand rows, SWIZZLE_64B / SWIZZLE_128B
 constexpr int AKS = AK / BK;   // K=16 steps per A chunk
 constexpr int NA = GP_STU_NA;  // A chunk buffers
-constexpr int EDGE = GP_STU_EDGE < NA - 1 ? GP_STU_EDGE : NA - 2;  // an edge block keeps <= EDGE + 1 chunks resident and
-                                                                   // one more buffer stays free for the gather's lag
+constexpr int EDGE = GP_STU_EDGE < NA ? GP_STU_EDGE : NA - 1;  // an edge block keeps EDGE (+1 when K is not a multiple of
+                                                               // the chunk) buffers resident; the gather hands over its
+                                                               // lagged chunk before it blocks, so NA buffers suffice
 
 // Order of the (column half h, K-steps) units of one tile, shared by the TMA producer and the MMA issuer.
 // N <= 256 (NH = 1): K ascending.  N = 512 (NH = 2 halves of 256 columns, each with its own full/empty barriers):

@@ -8,6 +8,7 @@
 //   2: 4 rows x 128 B (STG.128, eight lanes per row -- the round-1 smem-transposed epilogue)
 //   3: 2 rows x 256 B (STG.128)
 //   4: 1 row  x 512 B (STG.128, fully coalesced)
+//   5: cp.async.bulk shared -> global, 16 KB per copy, issued by one thread (the TMA engine instead of the LSU)
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o scripts/probes/store_bw scripts/probes/store_bw.cu
 #include <cstdio>
 #include <cstdint>
@@ -47,6 +48,52 @@ __global__ void __launch_bounds__(256) store_kernel(float* out, int tiles_per_ct
   if (threadIdx.x == 0) clk[blockIdx.x] = t1 - t0;
 }
 
+// pattern 5: the TMA engine instead of the LSU -- one thread issues cp.async.bulk shared -> global copies of 16 KB
+__global__ void __launch_bounds__(128) bulk_store_kernel(float* out, int tiles_per_cta, long long* clk) {
+  extern __shared__ __align__(128) unsigned char sm[];
+  for (int i = threadIdx.x; i < 32768 / 4; i += blockDim.x) ((float*)sm)[i] = (float)i;
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+  const long long t0 = clock64();
+  if (threadIdx.x == 0) {
+    const unsigned s0 = (unsigned)__cvta_generic_to_shared(sm);
+    for (int t = 0; t < tiles_per_cta; ++t) {
+      char* tile = (char*)(out + ((size_t)blockIdx.x * tiles_per_cta + t) * ROWS * COLS);
+      for (int c = 0; c < 16; ++c) {
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], 16384;" ::"l"(tile + c * 16384),
+                     "r"(s0 + (c & 1) * 16384)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 4;" ::: "memory");
+      }
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  __syncthreads();
+  const long long t1 = clock64();
+  if (threadIdx.x == 0) clk[blockIdx.x] = t1 - t0;
+}
+
+void run_bulk(float* buf, long long* clk, int grid, int tiles) {
+  cudaFuncSetAttribute(bulk_store_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768);
+  bulk_store_kernel<<<grid, 128, 32768>>>(buf, tiles, clk);
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  cudaEventRecord(e0);
+  bulk_store_kernel<<<grid, 128, 32768>>>(buf, tiles, clk);
+  cudaEventRecord(e1);
+  cudaDeviceSynchronize();
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  long long h[256], mx = 0;
+  cudaMemcpy(h, clk, sizeof(long long) * grid, cudaMemcpyDeviceToHost);
+  for (int i = 0; i < grid; ++i) mx = h[i] > mx ? h[i] : mx;
+  const double bytes = (double)tiles * ROWS * COLS * 4;
+  printf("pattern 5 (cp.async.bulk smem->global)  grid %3d : %7.1f B/clk/SM  (%.0f clk per 256 KB tile)  aggregate %6.0f GB/s  err=%s\n",
+         grid, bytes / (double)mx, (double)mx / tiles, bytes * grid / ms / 1e6, cudaGetErrorString(cudaGetLastError()));
+}
+
 template <int PAT>
 void run(float* buf, long long* clk, int grid, int threads, int tiles) {
   store_kernel<PAT><<<grid, threads>>>(buf, tiles, clk);  // warm-up
@@ -75,7 +122,8 @@ int main() {
   cudaMalloc(&buf, (size_t)148 * tiles * ROWS * COLS * 4);
   cudaMalloc(&clk, 256 * sizeof(long long));
   for (int grid : {148, 1}) {
-    for (int threads : {128, 256}) {
+    run_bulk(buf, clk, grid, tiles);
+    for (int threads : {128}) {
       run<0>(buf, clk, grid, threads, tiles);
       run<1>(buf, clk, grid, threads, tiles);
       run<2>(buf, clk, grid, threads, tiles);
