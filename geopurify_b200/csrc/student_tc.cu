@@ -9,10 +9,12 @@
 //      CTA iteration.  A rows are gathered with cp.async (zero-filled tails) from activations stored as bf16 hi/lo
 //      planes, in K=64 chunks laid out as 128-byte-swizzled K-major rows: 8 consecutive lanes fetch one 128-byte
 //      line of one row, so a warp-wide cp.async touches 4 cache lines (the first version fetched 16 bytes from 32
-//      different rows per instruction and was bound by the L1TEX tag stage at 85 %).  W_o^T slices arrive by TMA in
-//      K=16 stages (32-byte swizzle) from a pre-tiled weight image in which every stage's box is contiguous.  Each
-//      K=16 step issues  Alo*Bhi + Ahi*Blo + Ahi*Bhi  into a 128 x N fp32 accumulator in TMEM; the epilogue warps
-//      drain TMEM to a pair-major staging buffer with coalesced 128-byte row stores.
+//      different rows per instruction and was bound by the L1TEX tag stage at 85 %).  W_o^T slices arrive by TMA
+//      (32-byte swizzle) from a pre-tiled weight image in which every K=16 box is contiguous; a stage holds GP_STU_UK = 4
+//      K-steps of one 256-column half, so the MMA issuer pays one wait + fence + commit per 12 MMAs.  Each K=16 step
+//      issues  Alo*Bhi + Ahi*Blo + Ahi*Bhi  into a 128 x N fp32 accumulator in TMEM (two 256-column halves with their
+//      own full/empty barriers); the epilogue warps drain TMEM to a pair-major staging buffer straight from the
+//      accumulator fragments (tcgen05.ld.16x256b, float2 sector stores).
 //   3. reduce (student_reduce_kernel): out[i] = sum of its staged pair rows in ascending offset order (the oracle's
 //      order, deterministic, no atomics), BN scale/shift, residual, ReLU, then the bf16 hi/lo split for the next layer.
 #include <cub/device/device_scan.cuh>
