@@ -329,13 +329,16 @@ def fixed_list_arm(args, torch, dist, rank, world, local, model, hosts, resident
         tot = max(float(b[0]) for b in busy)
         return tot, [round(float(b[1]), 2) for b in busy]
 
-    l0 = _lib.launch_count
-    allocs0 = torch.cuda.memory_stats().get("num_device_alloc", 0)
-    sampler.mark_begin()
+    inter = None
     if args.streams > 1:
         from geopurify_b200.affinity_module import InterleavedScenes
         inter = InterleavedScenes(model, args.streams)
-        inter.run([resident[i] for i in range(len(hosts))], hist=hist, ignore=ign)     # warm the side streams
+        inter.run([resident[i] for i in range(len(hosts))], hist=hist, ignore=ign)     # warm the side streams' arenas:
+        torch.cuda.synchronize()                                                       # outside the counted region
+    l0 = _lib.launch_count
+    allocs0 = torch.cuda.memory_stats().get("num_device_alloc", 0)
+    sampler.mark_begin()
+    if inter is not None:
         ms, busy = timed(lambda: inter.run([resident[a] for a in seq], hist=hist, ignore=ign, collect=False))
     else:
         def body_seq():
