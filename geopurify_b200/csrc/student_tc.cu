@@ -56,6 +56,9 @@ constexpr int ROWB = BK * 2;   // bytes per operand row per stage
 #define PROF_T0()
 #define PROF_ADD(acc)
 #endif
+#ifndef GP_STU_EPI_PIPE
+#define GP_STU_EPI_PIPE 1  // direct epilogue: next TMEM fragment load in flight while the current one is stored
+#endif
 #ifndef GP_STU_ABLATE
 #define GP_STU_ABLATE 0  // 1 / 2: diagnostic builds (wrong results) whose epilogue skips the stores / the TMEM loads too
 #endif
@@ -397,32 +400,55 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
         float* crow = P.c + ((int64_t)ti.c_row0 + q * 32) * P.ldc + h * UN;
 #if GP_STU_EPI_DIRECT
         // accumulator-fragment loads: four threads hold one 32-byte sector of a row, stored as float2 straight from
-        // the registers -- no shared-memory transpose (the smem port is shared with the MMAs' operand reads)
-#pragma unroll 1
-        for (int hb = 0; hb < 2; ++hb) {
-          const int ra = hb * 16 + (lane >> 2), rb = ra + 8;
-          float* pa = crow + (int64_t)ra * P.ldc + 2 * (lane & 3);
-          float* pb2 = crow + (int64_t)rb * P.ldc + 2 * (lane & 3);
-#pragma unroll 1
-          for (int cg = 0; cg < UN / 64; ++cg) {
-            uint32_t v[32];
-            tc::tmem_ld_16x256b_x8(tacc + ((uint32_t)(q * 32 + hb * 16) << 16) + cg * 64, v);
-            tc::tmem_ld_wait();
-            if (hb == 1 && cg == UN / 64 - 1) release();
+        // the registers -- no shared-memory transpose (the smem port is shared with the MMAs' operand reads).
+        // Software-pipelined over two register sets (GP_STU_EPI_PIPE): the TMEM load of fragment i + 1 is in flight
+        // while fragment i is being stored.
+        constexpr int NI = 2 * (UN / 64);  // fragments per accumulator: 16 rows x 64 columns each
+        auto ldv = [&](int i, uint32_t(&v)[32]) {
+          const int hb = i / (UN / 64), cg = i % (UN / 64);
+          tc::tmem_ld_16x256b_x8(tacc + ((uint32_t)(q * 32 + hb * 16) << 16) + cg * 64, v);
+        };
+        auto stv = [&](int i, const uint32_t(&v)[32]) {
 #if GP_STU_ABLATE == 1
-            if (v[0] == 0x7fc12345u && v[31] == 0x7fc54321u) pa[0] = 1.f;
-            continue;
+          if (v[0] == 0x7fc12345u && v[31] == 0x7fc54321u) crow[0] = 1.f;
+          return;
 #endif
+          const int hb = i / (UN / 64), cg = i % (UN / 64);
+          const int ra = hb * 16 + (lane >> 2), rb = ra + 8;
+          float* pa = crow + (int64_t)ra * P.ldc + 2 * (lane & 3) + cg * 64;
+          float* pb2 = crow + (int64_t)rb * P.ldc + 2 * (lane & 3) + cg * 64;
 #pragma unroll
-            for (int g = 0; g < 8; ++g) {
-              const int col = cg * 64 + g * 8;
-              if (ra < rows_here)
-                *(float2*)(pa + col) = make_float2(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]));
-              if (rb < rows_here)
-                *(float2*)(pb2 + col) = make_float2(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
-            }
+          for (int g = 0; g < 8; ++g) {
+            if (ra < rows_here)
+              *(float2*)(pa + g * 8) = make_float2(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]));
+            if (rb < rows_here)
+              *(float2*)(pb2 + g * 8) = make_float2(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
           }
+        };
+#if GP_STU_EPI_PIPE
+        static_assert(NI % 2 == 0, "two fragments per pipeline round");
+        uint32_t va[32], vb[32];
+        ldv(0, va);
+#pragma unroll
+        for (int i = 0; i < NI; i += 2) {
+          tc::tmem_ld_wait();
+          ldv(i + 1, vb);
+          stv(i, va);
+          tc::tmem_ld_wait();
+          if (i + 2 < NI) ldv(i + 2, va);
+          else release();  // every TMEM read of this warp has completed
+          stv(i + 1, vb);
         }
+#else
+#pragma unroll 1
+        for (int i = 0; i < NI; ++i) {
+          uint32_t v[32];
+          ldv(i, v);
+          tc::tmem_ld_wait();
+          if (i == NI - 1) release();
+          stv(i, v);
+        }
+#endif
 #else
         for (int ch = 0; ch < UN / 32; ++ch) {
           uint32_t v[32];
