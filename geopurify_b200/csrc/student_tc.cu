@@ -56,6 +56,10 @@ constexpr int ROWB = BK * 2;   // bytes per operand row per stage
 #define PROF_T0()
 #define PROF_ADD(acc)
 #endif
+#ifndef GP_STU_EPI_QUAD
+#define GP_STU_EPI_QUAD 0  // direct epilogue: quad transpose by shuffles, 64 contiguous bytes per quad and STG.128.
+                           // Measured: 11.7 vs 10.8 ms -- the shuffle latency chains cost more than the wider stores give
+#endif
 #ifndef GP_STU_EPI_PIPE
 #define GP_STU_EPI_PIPE 1  // direct epilogue: next TMEM fragment load in flight while the current one is stored
 #endif
@@ -106,7 +110,16 @@ constexpr int CL = GP_STU_CL;  // 2: CTA pairs (cta_group::2).  Two tiles of one
 constexpr bool PAIR = CL == 2;
 constexpr int ALAG = 1;        // A chunks in flight per gather thread besides the one being issued
 constexpr int EPI_LD = 36;     // floats per staged row in the epilogue transpose buffer (16-byte aligned, conflict-free)
-constexpr int NTHREADS = 384;  // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue, 8-11 A gather
+#ifndef GP_STU_EPI2
+#define GP_STU_EPI2 0  // 1: a second set of four epilogue warps (12-15).  Set e drains accumulator e (N = 512: column half e;
+                       // N <= 256: the tiles that use accumulator e), so both halves are stored at the same time.
+                       // Measured: 10.78-10.83 vs 10.79-10.83 ms, no difference: each set then drains its half in 19k
+                       // clk -- the store path, not the number of warps, is the limit
+#endif
+constexpr bool EPI2 = GP_STU_EPI2 != 0;
+static_assert(!EPI2 || GP_STU_EPI_DIRECT, "the second epilogue set has no transpose buffer: direct epilogue only");
+constexpr int NTHREADS = EPI2 ? 512 : 384;  // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue (set 0), 8-11 A gather,
+                                            // 12-15 epilogue set 1
 
 struct TileInfo {  // one 128-pair tile
   int offset;      // kernel offset o (selects W_o)
@@ -330,7 +343,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
       printf("PROF mma: total %lld clk, tiles %u, wait tmem_empty %lld a_full %lld b_full %lld\n", clock64() - prof_start,
              tcount, w_te, w_af, w_bf);
 #endif
-  } else if (warp >= 4 && warp < 8) {
+  } else if ((warp >= 4 && warp < 8) || warp >= 12) {
     // ===================== epilogue: TMEM -> registers -> global rows, one accumulator (half) at a time ==============
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
     [[maybe_unused]] float* buf = epi + q * 32 * EPI_LD;
@@ -342,6 +355,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
       const int rows_here = ti.nrows - q * 32;  // valid rows in this warp's quadrant
       for (int h = 0; h < NH; ++h) {
         const int pb = part_bar(tcount, h);
+        if (EPI2 && pb != (warp >= 12)) continue;  // the other set's accumulator
         const uint32_t tacc = tmem_base + part_col(tcount, h);
         {
           PROF_T0();
@@ -415,6 +429,45 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
 #endif
           const int hb = i / (UN / 64), cg = i % (UN / 64);
           const int ra = hb * 16 + (lane >> 2), rb = ra + 8;
+#if GP_STU_EPI_QUAD
+          // 4 x 4 transpose inside every quad (two shfl.xor rounds): thread j ends up with the 16 CONSECUTIVE columns
+          // 16 j .. 16 j + 15 of its row, so a quad stores 64 contiguous bytes per STG.128 instead of four 8-byte pieces
+          // of one 32-byte sector per STG.64 (all SMs storing at once: 22 vs 19.4 B/clk/SM, scripts/probes/store_bw.cu)
+          const bool o = lane & 1, hq = (lane >> 1) & 1;
+#pragma unroll
+          for (int rs = 0; rs < 2; ++rs) {
+            // X[a][e]: block a = columns 16 a + {2 j, 2 j + 1, 8 + 2 j, 9 + 2 j}
+            uint32_t T[2][2][4], Y[4][4];
+#pragma unroll
+            for (int r = 0; r < 2; ++r)
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const uint32_t x0 = v[4 * (2 * (2 * r) + (e >> 1)) + rs * 2 + (e & 1)];      // block 2 r
+                const uint32_t x1 = v[4 * (2 * (2 * r + 1) + (e >> 1)) + rs * 2 + (e & 1)];  // block 2 r + 1
+                const uint32_t send = o ? x0 : x1, keep = o ? x1 : x0;
+                const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 1);
+                T[0][r][e] = o ? recv : keep;  // from the quad thread with bit 0 clear
+                T[1][r][e] = o ? keep : recv;  // from the one with bit 0 set
+              }
+#pragma unroll
+            for (int sbit = 0; sbit < 2; ++sbit)
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const uint32_t send = hq ? T[sbit][0][e] : T[sbit][1][e], keep = hq ? T[sbit][1][e] : T[sbit][0][e];
+                const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 2);
+                Y[sbit][e] = hq ? recv : keep;      // source thread with bit 1 clear
+                Y[2 + sbit][e] = hq ? keep : recv;  // source thread with bit 1 set
+              }
+            const int row = rs ? rb : ra;
+            if (row < rows_here) {
+              float4* dst = (float4*)(crow + (int64_t)row * P.ldc + cg * 64 + 16 * (lane & 3));
+              dst[0] = make_float4(__uint_as_float(Y[0][0]), __uint_as_float(Y[0][1]), __uint_as_float(Y[1][0]), __uint_as_float(Y[1][1]));
+              dst[1] = make_float4(__uint_as_float(Y[2][0]), __uint_as_float(Y[2][1]), __uint_as_float(Y[3][0]), __uint_as_float(Y[3][1]));
+              dst[2] = make_float4(__uint_as_float(Y[0][2]), __uint_as_float(Y[0][3]), __uint_as_float(Y[1][2]), __uint_as_float(Y[1][3]));
+              dst[3] = make_float4(__uint_as_float(Y[2][2]), __uint_as_float(Y[2][3]), __uint_as_float(Y[3][2]), __uint_as_float(Y[3][3]));
+            }
+          }
+#else
           float* pa = crow + (int64_t)ra * P.ldc + 2 * (lane & 3) + cg * 64;
           float* pb2 = crow + (int64_t)rb * P.ldc + 2 * (lane & 3) + cg * 64;
 #pragma unroll
@@ -424,6 +477,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
             if (rb < rows_here)
               *(float2*)(pb2 + g * 8) = make_float2(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
           }
+#endif
         };
 #if GP_STU_EPI_PIPE
         static_assert(NI % 2 == 0, "two fragments per pipeline round");
@@ -478,7 +532,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_tc_kernel(const __gri
     if (blockIdx.x == 0 && threadIdx.x == 128 && N == 512)
       printf("PROF epi: total %lld clk, wait tmem_full %lld (the rest is draining)\n", clock64() - prof_start, w_tf);
 #endif
-  } else if (warp >= 8) {
+  } else if (warp >= 8 && warp < 12) {
     // ===================== A gather: warp w owns tile rows [32 w, 32 w + 32); 8 lanes fetch one 128-byte row slice ====
     const int w = warp - 8;
     constexpr int LPR = AK * 2 / 16;   // lanes per row slice (16-byte chunks in AK bf16)

@@ -48,6 +48,49 @@ __global__ void __launch_bounds__(256) store_kernel(float* out, int tiles_per_ct
   if (threadIdx.x == 0) clk[blockIdx.x] = t1 - t0;
 }
 
+// pattern 0 again, with four MORE warps of the CTA gathering 128-byte lines by cp.async at full rate meanwhile (what the
+// GEMM's gather warps do at the start of a drain): does load traffic through the LSU slow the stores down?
+__global__ void __launch_bounds__(256) store_with_gather_kernel(float* out, const uint4* src, size_t src_lines,
+                                                                int tiles_per_cta, long long* clk, volatile int* stop) {
+  __shared__ __align__(128) unsigned char ring[32768];
+  __shared__ int done;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) done = 0;
+  __syncthreads();
+  if (warp < 4) {
+    const int q = warp;
+    const float v = (float)threadIdx.x;
+    const long long t0 = clock64();
+    for (int t = 0; t < tiles_per_cta; ++t) {
+      float* tile = out + ((size_t)blockIdx.x * tiles_per_cta + t) * ROWS * COLS + (size_t)q * 32 * COLS;
+      for (int hb = 0; hb < 2; ++hb)
+        for (int c0 = 0; c0 < COLS; c0 += 8) {
+          float* p = tile + (size_t)(hb * 16 + (lane >> 2)) * COLS + c0 + 2 * (lane & 3);
+          *(float2*)p = make_float2(v, v);
+          *(float2*)(p + 8 * COLS) = make_float2(v, v);
+        }
+    }
+    const long long t1 = clock64();
+    if (lane == 0) {
+      atomicMax((unsigned long long*)&clk[blockIdx.x], (unsigned long long)(t1 - t0));
+      atomicAdd(&done, 1);
+    }
+  } else {
+    unsigned long long x = blockIdx.x * 977 + threadIdx.x / 8;
+    const unsigned s0 = (unsigned)__cvta_generic_to_shared(ring);
+    int it = 0;
+    while (*(volatile int*)&done < 4) {
+      x = x * 6364136223846793005ull + 1442695040888963407ull;
+      const uint4* g = src + ((x >> 20) % src_lines) * 8 + (lane & 7);   // 8 lanes share one 128-byte line
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s0 + ((it & 15) * 2048 + threadIdx.x % 128 * 16)), "l"(g));
+      asm volatile("cp.async.commit_group;");
+      asm volatile("cp.async.wait_group 8;");
+      ++it;
+    }
+    asm volatile("cp.async.wait_group 0;");
+  }
+}
+
 // pattern 5: the TMA engine instead of the LSU -- one thread issues cp.async.bulk shared -> global copies of 16 KB
 __global__ void __launch_bounds__(128) bulk_store_kernel(float* out, int tiles_per_cta, long long* clk) {
   extern __shared__ __align__(128) unsigned char sm[];
@@ -122,6 +165,16 @@ int main() {
   cudaMalloc(&buf, (size_t)148 * tiles * ROWS * COLS * 4);
   cudaMalloc(&clk, 256 * sizeof(long long));
   for (int grid : {148, 1}) {
+    {
+      cudaMemset(clk, 0, 256 * sizeof(long long));
+      store_with_gather_kernel<<<grid, 256>>>(buf, (const uint4*)buf, (size_t)148 * tiles * ROWS * COLS * 4 / 128, tiles, clk, nullptr);
+      cudaDeviceSynchronize();
+      long long h[256], mx = 0;
+      cudaMemcpy(h, clk, sizeof(long long) * grid, cudaMemcpyDeviceToHost);
+      for (int i = 0; i < grid; ++i) mx = h[i] > mx ? h[i] : mx;
+      printf("pattern 0 + 4 gather warps (cp.async)  grid %3d : %7.1f B/clk/SM  (%.0f clk per 256 KB tile)  err=%s\n", grid,
+             (double)tiles * ROWS * COLS * 4 / (double)mx, (double)mx / tiles, cudaGetErrorString(cudaGetLastError()));
+    }
     run_bulk(buf, clk, grid, tiles);
     for (int threads : {128}) {
       run<0>(buf, clk, grid, threads, tiles);
