@@ -97,3 +97,20 @@ def test_intrinsic_helpers_match_reference_golden():
             assert (np.asarray(k) == np.asarray(c["make"])).all()
             a = mod.adjust_intrinsic(np.asarray(k).copy(), c["src"], c["dst"])
             assert (np.asarray(a) == np.asarray(c["adjust"])).all()
+
+
+def test_static_scratch_entry_point_limits_without_a_gpu():
+    """gp_scatter_mean_static rejects sizes beyond its stated maximum before it touches CUDA, and the limits the GPU
+    test file assumes are the header's."""
+    src = open(os.path.join(ROOT, "include", "geopurify_b200.h")).read()
+    lim = {k: int(v) for k, v in re.findall(r"#define (GP_SCATTER_STATIC_MAX_[NM]) (\d+)", src)}
+    assert lim == {"GP_SCATTER_STATIC_MAX_N": 262144, "GP_SCATTER_STATIC_MAX_M": 262144}
+    assert re.search(r"#define GP_SCATTER_STATIC_BYTES \(16 \* 1024 \* 1024\)", src)
+    zz = open(os.path.join(ROOT, "tests", "test_zz_no_alloc.py")).read()
+    assert "MAX_N = 262144" in zz and "MAX_M = 262144" in zz
+    lib = _lib.load()
+    for n, m in ((lim["GP_SCATTER_STATIC_MAX_N"] + 1, 8), (8, lim["GP_SCATTER_STATIC_MAX_M"] + 1)):
+        rc = lib.gp_scatter_mean_static(None, n, m, None, 4, 4, None, 4, 0, None)
+        assert rc == 1 and b"beyond the static scratch limits" in lib.gp_last_error()
+    rc = lib.gp_scatter_mean_static(None, 8, 8, None, 2, 4, None, 4, 0, None)   # src_stride < D
+    assert rc == 1 and b"bad sizes" in lib.gp_last_error()
